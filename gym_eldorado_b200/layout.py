@@ -1,0 +1,136 @@
+"""Exported record layouts (the wire format of the drop-in boundary).
+
+These numpy structured dtypes restate the reference's POD records byte for byte
+(reference include/api.h:67-161, dtype registration src/pybind/common.cpp:8-20;
+offsets as measured on x86-64 with a 64-byte interference size).
+The same numbers are `static_assert`ed on the device side in csrc/cog_layout.h.
+
+Only payload bytes are meaningful: record padding is indeterminate in the
+reference and is never compared.
+"""
+import numpy as np
+
+GRIDSIZE = 48
+N_MAP_FEATURES = 7
+N_CARDTYPES = 21
+N_BUYABLETYPES = 18
+N_DIRECTIONS = 7
+N_RESOURCETYPES = 3
+MAX_N_PLAYERS = 4
+
+# Difficulty (include/constants.h:11)
+EASY, MEDIUM, HARD = 0, 1, 2
+# TurnPhase (include/constants.h:76)
+INACTIVE, MOVEMENT, BUYING = 0, 1, 2
+
+deck_obs_dtype = np.dtype({
+    "names": ["draw", "hand", "active", "played", "discard"],
+    "formats": [(np.uint8, (N_CARDTYPES,))] * 5,
+    "offsets": [0, 21, 42, 63, 84],
+    "itemsize": 105,
+})
+
+action_mask_dtype = np.dtype({
+    "names": ["play", "play_special", "remove", "move", "get_from_shop"],
+    "formats": [(np.bool_, (N_CARDTYPES + 1,)), (np.bool_, (N_CARDTYPES + 1,)),
+                (np.bool_, (N_CARDTYPES + 1,)), (np.bool_, (N_DIRECTIONS,)),
+                (np.bool_, (N_BUYABLETYPES + 1,))],
+    "offsets": [0, 22, 44, 66, 73],
+    "itemsize": 128,
+})
+ACTION_MASK_PAYLOAD = 92
+
+player_data_dtype = np.dtype({
+    "names": ["obs", "action_mask"],
+    "formats": [deck_obs_dtype, action_mask_dtype],
+    "offsets": [0, 128],
+    "itemsize": 256,
+})
+
+shared_obs_dtype = np.dtype({
+    "names": ["map", "phase", "current_resources", "shop"],
+    "formats": [(np.uint8, (GRIDSIZE, GRIDSIZE, N_MAP_FEATURES)), np.uint8,
+                (np.float32, (N_RESOURCETYPES,)), (np.uint8, (N_BUYABLETYPES,))],
+    "offsets": [0, 16128, 16132, 16144],
+    "itemsize": 16164,
+})
+
+obs_dtype = np.dtype({
+    "names": ["shared", "player_data"],
+    "formats": [shared_obs_dtype, (player_data_dtype, (MAX_N_PLAYERS,))],
+    "offsets": [0, 16192],
+    "itemsize": 17216,
+})
+
+action_dtype = np.dtype({
+    "names": ["play", "play_special", "remove", "move", "get_from_shop"],
+    "formats": [np.uint8] * 5,
+    "offsets": [0, 1, 2, 3, 4],
+    "itemsize": 64,
+})
+ACTION_PAYLOAD = 5
+
+agent_info_dtype = np.dtype({
+    "names": ["steps_taken", "returns", "travelled_hexes", "cards_added",
+              "cards_removed", "n_machete_uses", "n_paddle_uses", "n_coin_uses",
+              "n_card_uses"],
+    "formats": [np.uint8, np.float32, np.uint32, np.uint8, np.uint8, np.uint32,
+                np.uint32, np.uint32, np.uint32],
+    "offsets": [0, 4, 8, 12, 13, 16, 20, 24, 28],
+    "itemsize": 32,
+})
+
+info_dtype = np.dtype({
+    "names": ["total_length", "agent_infos"],
+    "formats": [np.uint32, (agent_info_dtype, (MAX_N_PLAYERS,))],
+    "offsets": [0, 4],
+    "itemsize": 192,
+})
+
+# Which exported buffer is which (shared with include/cog_b200.h: enum cog_buffer)
+BUF_OBS, BUF_SELECTED_MASKS, BUF_REWARDS, BUF_DONES, BUF_INFOS, BUF_AGENT_SELECTION = range(6)
+
+BUFFER_DTYPES = {
+    BUF_OBS: obs_dtype,
+    BUF_SELECTED_MASKS: action_mask_dtype,
+    BUF_REWARDS: np.dtype((np.float32, (MAX_N_PLAYERS,))),
+    BUF_DONES: np.dtype(np.bool_),
+    BUF_INFOS: info_dtype,
+    BUF_AGENT_SELECTION: np.dtype(np.uint8),
+}
+
+
+def payload_bytes(arr):
+    """Concatenate the payload (non-padding) bytes of a structured array.
+
+    Returns a uint8 array of shape (len(arr), n_payload_bytes); used by the
+    parity tests so padding never takes part in a comparison.
+    """
+    arr = np.ascontiguousarray(arr)
+    n = arr.shape[0] if arr.ndim else 1
+    raw = arr.reshape(n, -1) if arr.dtype.names is None else arr.reshape(n)
+    if arr.dtype.names is None:
+        return raw.view(np.uint8).reshape(n, -1)
+    cols = []
+
+    def walk(dt, base, view):
+        if dt.names is None:
+            sub = dt.subdtype
+            if sub is not None:
+                elem, shape = sub
+                count = int(np.prod(shape))
+                if elem.names is None:
+                    cols.append(view[:, base:base + elem.itemsize * count])
+                else:
+                    for k in range(count):
+                        walk(elem, base + k * elem.itemsize, view)
+            else:
+                cols.append(view[:, base:base + dt.itemsize])
+            return
+        for name in dt.names:
+            fdt, off = dt.fields[name][:2]
+            walk(fdt, base + off, view)
+
+    bytes_view = raw.view(np.uint8).reshape(n, arr.dtype.itemsize)
+    walk(arr.dtype, 0, bytes_view)
+    return np.concatenate(cols, axis=1)
