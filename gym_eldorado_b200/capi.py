@@ -1,0 +1,197 @@
+"""ctypes binding of the C ABI in include/cog_b200.h (libcog_b200.so).
+
+This is the thin layer every Python-side caller goes through; the pybind11 module
+(csrc/pybind_module.cpp) binds the same symbols from C++.  There is no fallback: if
+the CUDA library is missing or cannot be loaded, importing the handles below raises.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from . import layout
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcog_b200.so")
+
+COG_OK = 0
+COG_ERR_INVALID, COG_ERR_MAP_FAILURE, COG_ERR_MAP_BOUNDS, COG_ERR_CUDA, COG_ERR_NOT_RESET = -1, -2, -3, -4, -5
+STAT_NAMES = ("env_steps", "episodes", "truncations", "total_length", "wins_seat0", "wins_seat1",
+              "wins_seat2", "wins_seat3", "travelled_hexes", "cards_added", "resets", "reserved")
+
+# every symbol include/cog_b200.h declares: name -> (restype, argtypes)
+_vp, _u64, _u32, _u8, _int, _sz = (ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_uint8,
+                                    ctypes.c_int, ctypes.c_size_t)
+_P = ctypes.POINTER
+SYMBOLS = {
+    "cog_last_error": (ctypes.c_char_p, []),
+    "cog_device_count": (_int, [_P(_int)]),
+    "cog_vec_create": (_int, [_u64, _u64, _int, _vp, _P(_vp)]),
+    "cog_vec_destroy": (_int, [_vp]),
+    "cog_vec_reset": (_int, [_vp, _u32, _u8, _u8, _int, _u32, _int]),
+    "cog_vec_reset_default": (_int, [_vp]),
+    "cog_vec_step": (_int, [_vp, _vp]),
+    "cog_vec_step_host": (_int, [_vp, _vp]),
+    "cog_vec_buffer": (_int, [_vp, _int, _P(_vp), _P(_sz), _P(_sz)]),
+    "cog_vec_read": (_int, [_vp, _int, _vp, _sz]),
+    "cog_vec_num_envs": (_int, [_vp, _P(_u64)]),
+    "cog_sampler_create": (_int, [_u64, _u64, _u32, _int, _vp, _P(_vp)]),
+    "cog_sampler_destroy": (_int, [_vp]),
+    "cog_sampler_sample": (_int, [_vp, _vp]),
+    "cog_sampler_sample_host": (_int, [_vp, _vp]),
+    "cog_sampler_actions": (_int, [_vp, _P(_vp)]),
+    "cog_sampler_read_actions": (_int, [_vp, _vp, _sz]),
+    "cog_vec_run_fused": (_int, [_vp, _vp, _u64]),
+    "cog_vec_stats": (_int, [_vp, _P(_u64), _sz]),
+    "cog_vec_stats_reset": (_int, [_vp]),
+    "cog_sync": (_int, [_vp]),
+    "cog_kernel_launches": (_u64, []),
+    "cog_vec_last_kernel_ms": (_int, [_vp, _P(ctypes.c_float)]),
+}
+
+
+class CogError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(message)
+        self.code = code
+
+
+class MapGenerationError(CogError):
+    """generate_map_failure (reference include/map.h:13-15 -> Python RuntimeError)."""
+
+
+def load(path=LIB_PATH):
+    """dlopen the library and declare every prototype. Raises if it is absent."""
+    if not os.path.exists(path):
+        raise ImportError(
+            "%s is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). There is no CPU fallback." % path)
+    lib = ctypes.CDLL(path)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)  # AttributeError if the library does not export it
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = load()
+    return _lib
+
+
+def check(L, rc):
+    if rc == COG_OK:
+        return
+    msg = L.cog_last_error().decode()
+    if rc in (COG_ERR_MAP_FAILURE, COG_ERR_MAP_BOUNDS):
+        raise MapGenerationError(rc, msg)
+    raise CogError(rc, msg)
+
+
+class VecHandle:
+    """cog_vec: one GPU's slice of vec_cog_env (reference include/vec_environment.h:12-81)."""
+
+    def __init__(self, n_envs, env_index_offset=0, device=0, stream=None, library=None):
+        self.L = library or lib()
+        self.n = int(n_envs)
+        self.device = device
+        self.offset = env_index_offset
+        h = _vp()
+        check(self.L, self.L.cog_vec_create(self.n, env_index_offset, device, stream, ctypes.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.L.cog_vec_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def reset(self, seed=None, n_players=4, n_pieces=3, difficulty=0, max_steps=100000, render=False):
+        if seed is None:
+            check(self.L, self.L.cog_vec_reset_default(self._h))
+        else:
+            check(self.L, self.L.cog_vec_reset(self._h, int(seed) & 0xFFFFFFFF, n_players, n_pieces,
+                                               int(difficulty), max_steps, int(bool(render))))
+
+    def step_device(self, d_actions_ptr):
+        check(self.L, self.L.cog_vec_step(self._h, d_actions_ptr))
+
+    def step_host(self, actions):
+        assert actions.dtype == layout.action_dtype and actions.flags.c_contiguous and len(actions) == self.n
+        check(self.L, self.L.cog_vec_step_host(self._h, actions.ctypes.data))
+
+    def buffer(self, which):
+        """(device pointer, itemsize, count) of an exported buffer."""
+        p, item, cnt = _vp(), _sz(), _sz()
+        check(self.L, self.L.cog_vec_buffer(self._h, which, ctypes.byref(p), ctypes.byref(item), ctypes.byref(cnt)))
+        return p.value, item.value, cnt.value
+
+    def read(self, which, out=None):
+        """Device -> host copy of an exported buffer as a structured numpy array."""
+        dt = layout.BUFFER_DTYPES[which]
+        if out is None:
+            out = np.empty(self.n, dtype=dt)
+        check(self.L, self.L.cog_vec_read(self._h, which, out.ctypes.data, out.nbytes))
+        return out
+
+    def run_fused(self, sampler, k_steps):
+        check(self.L, self.L.cog_vec_run_fused(self._h, sampler._s, int(k_steps)))
+
+    def stats(self):
+        out = (_u64 * len(STAT_NAMES))()
+        check(self.L, self.L.cog_vec_stats(self._h, out, len(STAT_NAMES)))
+        return dict(zip(STAT_NAMES, (int(x) for x in out)))
+
+    def stats_reset(self):
+        check(self.L, self.L.cog_vec_stats_reset(self._h))
+
+    def sync(self):
+        check(self.L, self.L.cog_sync(self._h))
+
+    def last_kernel_ms(self):
+        ms = ctypes.c_float()
+        check(self.L, self.L.cog_vec_last_kernel_ms(self._h, ctypes.byref(ms)))
+        return ms.value
+
+
+class SamplerHandle:
+    """cog_sampler: vec_action_sampler (reference include/vec_sampler.h:7-27)."""
+
+    def __init__(self, n_envs, seed, env_index_offset=0, device=0, stream=None, library=None):
+        self.L = library or lib()
+        self.n = int(n_envs)
+        s = _vp()
+        check(self.L, self.L.cog_sampler_create(self.n, env_index_offset, int(seed) & 0xFFFFFFFF, device,
+                                                stream, ctypes.byref(s)))
+        self._s = s
+
+    def close(self):
+        if getattr(self, "_s", None):
+            self.L.cog_sampler_destroy(self._s)
+            self._s = None
+
+    __del__ = close
+
+    def sample_device(self, d_masks_ptr):
+        check(self.L, self.L.cog_sampler_sample(self._s, d_masks_ptr))
+
+    def sample_host(self, masks):
+        assert masks.dtype == layout.action_mask_dtype and masks.flags.c_contiguous and len(masks) == self.n
+        check(self.L, self.L.cog_sampler_sample_host(self._s, masks.ctypes.data))
+
+    def actions_ptr(self):
+        p = _vp()
+        check(self.L, self.L.cog_sampler_actions(self._s, ctypes.byref(p)))
+        return p.value
+
+    def read_actions(self, out=None):
+        if out is None:
+            out = np.empty(self.n, dtype=layout.action_dtype)
+        check(self.L, self.L.cog_sampler_read_actions(self._s, out.ctypes.data, out.nbytes))
+        return out

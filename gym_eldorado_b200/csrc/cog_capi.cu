@@ -1,0 +1,398 @@
+/* cog_capi.cu — host side of the C ABI declared in include/cog_b200.h.
+ *
+ * Owns the device buffers of a handle (exported records in the reference's layouts
+ * plus the private state), enqueues the kernels of cog_kernels.cuh on the handle's
+ * stream and surfaces device-side failures.  There is no CPU implementation behind
+ * this ABI: without a CUDA device every compute entry point fails with COG_ERR_CUDA.
+ *
+ * (tests/emu builds this same file against a lock-step warp emulator, with COG_EMU
+ * defined, to check the kernels' logic on machines without a GPU; that build is test
+ * infrastructure and is never loaded by the package.)
+ */
+#ifdef COG_EMU
+#include "cuda_emu.h"
+#else
+#include <cuda_runtime.h>
+#endif
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <random>
+#include <string>
+
+#include "cog_b200.h"
+#include "cog_kernels.cuh"
+
+#ifdef COG_EMU
+#define COG_LAUNCH(kernel, grid, block, smem, stream, ...) \
+  cuda_emu::launch((grid), (block), (smem), [&]() { kernel(__VA_ARGS__); })
+#else
+#define COG_LAUNCH(kernel, grid, block, smem, stream, ...) \
+  kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+#endif
+
+static_assert(COG_OBS_SIZE == COGL_OBS_SIZE && COG_MASK_SIZE == COGL_MASK_SIZE &&
+                  COG_ACTION_SIZE == COGL_ACTION_SIZE && COG_INFO_SIZE == COGL_INFO_SIZE,
+              "C ABI and kernel layouts disagree");
+static_assert(COG_STAT_COUNT == 12 && COG_STAT_RESETS == 10, "stat slots are hard-coded in the kernels");
+
+namespace {
+
+thread_local std::string g_error;
+std::atomic<uint64_t> g_launches{0};
+
+int fail(int code, const std::string &msg) {
+  g_error = msg;
+  return code;
+}
+int cuda_fail(cudaError_t e, const char *what) {
+  return fail(COG_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CK(call)                                        \
+  do {                                                  \
+    cudaError_t e_ = (call);                            \
+    if (e_ != cudaSuccess) return cuda_fail(e_, #call); \
+  } while (0)
+
+size_t scratch_bytes() { return sizeof(cog::BoardScratch) * cog::WARPS_PER_BLOCK; }
+unsigned blocks_for(uint64_t n) { return (unsigned)((n + cog::WARPS_PER_BLOCK - 1) / cog::WARPS_PER_BLOCK); }
+
+}  // namespace
+
+struct cog_vec {
+  uint64_t n = 0, offset = 0;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  cog::Buffers B{};
+  cog::Params prm{100000, 4, 3, 0}; /* cog_env::cog_env() defaults src/environment.cpp:10-15 */
+  bool seeded = false;
+  int sm_count = 1, fused_blocks_per_sm = 1;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool timed = false;
+  void *act_staging = nullptr; /* device copy of host actions for cog_vec_step_host */
+};
+
+struct cog_sampler {
+  uint64_t n = 0, offset = 0;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  uint32_t *srng = nullptr;
+  uint8_t *actions = nullptr;
+  void *staging = nullptr; /* device copy of host masks for cog_sampler_sample_host */
+};
+
+namespace {
+
+int check_device_error(cog_vec *h) {
+  int err[2] = {0, 0};
+  CK(cudaMemcpyAsync(err, h->B.err, sizeof(err), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  if (err[0] == 0) return COG_OK;
+  CK(cudaMemsetAsync(h->B.err, 0, sizeof(err), h->stream));
+  char msg[160];
+  if (err[0] == COG_ERR_MAP_FAILURE)
+    std::snprintf(msg, sizeof msg, "Failed to generate map in specified maximum number of attempts (env %d)", err[1]);
+  else
+    std::snprintf(msg, sizeof msg, "generated board does not fit the 48x48 observation (env %d)", err[1]);
+  return fail(err[0], msg);
+}
+
+void time_begin(cog_vec *h) { cudaEventRecord(h->ev0, h->stream); }
+void time_end(cog_vec *h) {
+  cudaEventRecord(h->ev1, h->stream);
+  h->timed = true;
+}
+
+int launch_reset(cog_vec *h, uint32_t seed, int reseed) {
+  CK(cudaSetDevice(h->device));
+  COG_LAUNCH(cog::k_reset, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm,
+             h->n, (uint64_t)seed + h->offset, reseed);
+  g_launches++;
+  CK(cudaGetLastError());
+  return check_device_error(h);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *cog_last_error(void) { return g_error.c_str(); }
+
+int cog_device_count(int *count) {
+  if (!count) return fail(COG_ERR_INVALID, "count is NULL");
+  CK(cudaGetDeviceCount(count));
+  return COG_OK;
+}
+
+uint64_t cog_kernel_launches(void) { return g_launches.load(); }
+
+int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device, void *stream, cog_vec **out) {
+  if (!out || n_envs == 0) return fail(COG_ERR_INVALID, "n_envs must be > 0 and out non-NULL");
+  CK(cudaSetDevice(device));
+  cog_vec *h = new (std::nothrow) cog_vec;
+  if (!h) return fail(COG_ERR_INVALID, "out of host memory");
+  h->n = n_envs;
+  h->offset = env_index_offset;
+  h->device = device;
+  h->stream = (cudaStream_t)stream; /* NULL = the device's default stream */
+  CK(cudaEventCreate(&h->ev0));
+  CK(cudaEventCreate(&h->ev1));
+  CK(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device));
+  const uint64_t n = n_envs;
+  struct { void **p; size_t bytes; } bufs[] = {
+      {(void **)&h->B.hidden, n * COG_HID_WORDS * sizeof(uint32_t)},
+      {(void **)&h->B.grid, n * COGL_GRID_BYTES},
+      {(void **)&h->B.obs, n * COG_OBS_SIZE},
+      {(void **)&h->B.masks, n * COG_MASK_SIZE},
+      {(void **)&h->B.rewards, n * 4 * sizeof(float)},
+      {(void **)&h->B.dones, n},
+      {(void **)&h->B.infos, n * COG_INFO_SIZE},
+      {(void **)&h->B.agents, n},
+      {(void **)&h->B.stats, COG_STAT_COUNT * sizeof(unsigned long long)},
+      {(void **)&h->B.err, 2 * sizeof(int)},
+  };
+  for (auto &b : bufs) {
+    cudaError_t e = cudaMalloc(b.p, b.bytes);
+    if (e == cudaSuccess) e = cudaMemsetAsync(*b.p, 0, b.bytes, h->stream);
+    if (e != cudaSuccess) {
+      cog_vec_destroy(h);
+      return cuda_fail(e, "cudaMalloc");
+    }
+  }
+#ifndef COG_EMU
+  CK(cudaFuncSetAttribute(cog::k_step<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
+  int per_sm = 0;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step<true>, cog::BLOCK_THREADS, scratch_bytes()));
+  h->fused_blocks_per_sm = per_sm > 0 ? per_sm : 1;
+#endif
+  COG_LAUNCH(cog::k_init, blocks_for(n), cog::BLOCK_THREADS, 0, h->stream, h->B, n);
+  g_launches++;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->stream));
+  *out = h;
+  return COG_OK;
+}
+
+int cog_vec_destroy(cog_vec *h) {
+  if (!h) return COG_OK;
+  cudaSetDevice(h->device);
+  cudaStreamSynchronize(h->stream);
+  void *ptrs[] = {h->B.hidden, h->B.grid, h->B.obs, h->B.masks, h->B.rewards,
+                  h->B.dones,  h->B.infos, h->B.agents, h->B.stats, h->B.err, h->act_staging};
+  for (void *p : ptrs)
+    if (p) cudaFree(p);
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+  return COG_OK;
+}
+
+int cog_vec_num_envs(cog_vec *h, uint64_t *n) {
+  if (!h || !n) return fail(COG_ERR_INVALID, "NULL argument");
+  *n = h->n;
+  return COG_OK;
+}
+
+int cog_vec_reset(cog_vec *h, uint32_t seed, uint8_t n_players, uint8_t n_pieces, int difficulty,
+                  uint32_t max_steps, int render) {
+  (void)render;
+  if (!h) return fail(COG_ERR_INVALID, "NULL handle");
+  if (n_players < 1 || n_players > COG_MAX_PLAYERS) return fail(COG_ERR_INVALID, "n_players must be 1..4");
+  if (difficulty < COG_EASY || difficulty > COG_HARD) return fail(COG_ERR_INVALID, "unknown difficulty");
+  h->prm.max_steps = max_steps;
+  h->prm.n_players = n_players;
+  h->prm.n_pieces = n_pieces;
+  h->prm.difficulty = (uint32_t)difficulty;
+  h->seeded = true;
+  return launch_reset(h, seed, 1);
+}
+
+int cog_vec_reset_default(cog_vec *h) {
+  if (!h) return fail(COG_ERR_INVALID, "NULL handle");
+  if (!h->seeded) { /* cog_env() seeds from std::random_device (src/environment.cpp:10-15) */
+    h->seeded = true;
+    return launch_reset(h, std::random_device{}(), 1);
+  }
+  return launch_reset(h, 0, 0);
+}
+
+int cog_vec_step(cog_vec *h, const void *d_actions) {
+  if (!h || !d_actions) return fail(COG_ERR_INVALID, "NULL argument");
+  if (!h->seeded) return fail(COG_ERR_NOT_RESET, "step() before reset()");
+  CK(cudaSetDevice(h->device));
+  time_begin(h);
+  COG_LAUNCH(cog::k_step<false>, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B,
+             h->prm, h->n, (const uint8_t *)d_actions, (uint32_t *)nullptr, (uint8_t *)nullptr, (uint64_t)1);
+  time_end(h);
+  g_launches++;
+  CK(cudaGetLastError());
+  return COG_OK;
+}
+
+int cog_vec_buffer(cog_vec *h, int which, void **d_ptr, size_t *itemsize, size_t *count) {
+  if (!h) return fail(COG_ERR_INVALID, "NULL handle");
+  void *p = nullptr;
+  size_t item = 0;
+  switch (which) {
+  case COG_BUF_OBS: p = h->B.obs; item = COG_OBS_SIZE; break;
+  case COG_BUF_SELECTED_MASKS: p = h->B.masks; item = COG_MASK_SIZE; break;
+  case COG_BUF_REWARDS: p = h->B.rewards; item = 4 * sizeof(float); break;
+  case COG_BUF_DONES: p = h->B.dones; item = 1; break;
+  case COG_BUF_INFOS: p = h->B.infos; item = COG_INFO_SIZE; break;
+  case COG_BUF_AGENT_SELECTION: p = h->B.agents; item = 1; break;
+  default: return fail(COG_ERR_INVALID, "unknown buffer id");
+  }
+  if (d_ptr) *d_ptr = p;
+  if (itemsize) *itemsize = item;
+  if (count) *count = (size_t)h->n;
+  return COG_OK;
+}
+
+int cog_vec_read(cog_vec *h, int which, void *h_dst, size_t nbytes) {
+  void *p;
+  size_t item, count;
+  int rc = cog_vec_buffer(h, which, &p, &item, &count);
+  if (rc) return rc;
+  if (!h_dst || nbytes > item * count) return fail(COG_ERR_INVALID, "bad destination / size");
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpyAsync(h_dst, p, nbytes, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return COG_OK;
+}
+
+int cog_sampler_create(uint64_t n_envs, uint64_t env_index_offset, uint32_t seed, int device, void *stream,
+                       cog_sampler **out) {
+  if (!out || n_envs == 0) return fail(COG_ERR_INVALID, "n_envs must be > 0 and out non-NULL");
+  CK(cudaSetDevice(device));
+  cog_sampler *s = new (std::nothrow) cog_sampler;
+  if (!s) return fail(COG_ERR_INVALID, "out of host memory");
+  s->n = n_envs;
+  s->offset = env_index_offset;
+  s->device = device;
+  s->stream = (cudaStream_t)stream; /* NULL = the device's default stream */
+  cudaError_t e = cudaMalloc((void **)&s->srng, n_envs * sizeof(uint32_t));
+  if (e == cudaSuccess) e = cudaMalloc((void **)&s->actions, n_envs * COG_ACTION_SIZE);
+  if (e == cudaSuccess) e = cudaMemsetAsync(s->actions, 0, n_envs * COG_ACTION_SIZE, s->stream);
+  if (e != cudaSuccess) {
+    cog_sampler_destroy(s);
+    return cuda_fail(e, "cudaMalloc");
+  }
+  COG_LAUNCH(cog::k_sampler_seed, (unsigned)((n_envs + 255) / 256), 256, 0, s->stream, s->srng, n_envs,
+             (uint64_t)seed + env_index_offset);
+  g_launches++;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(s->stream));
+  *out = s;
+  return COG_OK;
+}
+
+int cog_sampler_destroy(cog_sampler *s) {
+  if (!s) return COG_OK;
+  cudaSetDevice(s->device);
+  cudaStreamSynchronize(s->stream);
+  if (s->srng) cudaFree(s->srng);
+  if (s->actions) cudaFree(s->actions);
+  if (s->staging) cudaFree(s->staging);
+  if (s->own_stream && s->stream) cudaStreamDestroy(s->stream);
+  delete s;
+  return COG_OK;
+}
+
+int cog_sampler_sample(cog_sampler *s, const void *d_masks) {
+  if (!s || !d_masks) return fail(COG_ERR_INVALID, "NULL argument");
+  CK(cudaSetDevice(s->device));
+  COG_LAUNCH(cog::k_sample, blocks_for(s->n), cog::BLOCK_THREADS, 0, s->stream, (const uint8_t *)d_masks,
+             s->srng, s->actions, s->n);
+  g_launches++;
+  CK(cudaGetLastError());
+  return COG_OK;
+}
+
+int cog_sampler_sample_host(cog_sampler *s, const void *h_masks) {
+  if (!s || !h_masks) return fail(COG_ERR_INVALID, "NULL argument");
+  CK(cudaSetDevice(s->device));
+  if (!s->staging) CK(cudaMalloc(&s->staging, s->n * COG_MASK_SIZE));
+  CK(cudaMemcpyAsync(s->staging, h_masks, s->n * COG_MASK_SIZE, cudaMemcpyHostToDevice, s->stream));
+  return cog_sampler_sample(s, s->staging);
+}
+
+int cog_sampler_actions(cog_sampler *s, void **d_ptr) {
+  if (!s || !d_ptr) return fail(COG_ERR_INVALID, "NULL argument");
+  *d_ptr = s->actions;
+  return COG_OK;
+}
+
+int cog_sampler_read_actions(cog_sampler *s, void *h_dst, size_t nbytes) {
+  if (!s || !h_dst || nbytes > s->n * COG_ACTION_SIZE) return fail(COG_ERR_INVALID, "bad destination / size");
+  CK(cudaSetDevice(s->device));
+  CK(cudaMemcpyAsync(h_dst, s->actions, nbytes, cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  return COG_OK;
+}
+
+int cog_vec_step_host(cog_vec *h, const void *h_actions) {
+  if (!h || !h_actions) return fail(COG_ERR_INVALID, "NULL argument");
+  CK(cudaSetDevice(h->device));
+  const size_t bytes = h->n * COG_ACTION_SIZE;
+  if (!h->act_staging) CK(cudaMalloc(&h->act_staging, bytes));
+  CK(cudaMemcpyAsync(h->act_staging, h_actions, bytes, cudaMemcpyHostToDevice, h->stream));
+  return cog_vec_step(h, h->act_staging);
+}
+
+int cog_vec_run_fused(cog_vec *h, cog_sampler *s, uint64_t k_steps) {
+  if (!h || !s) return fail(COG_ERR_INVALID, "NULL argument");
+  if (s->n != h->n || s->device != h->device) return fail(COG_ERR_INVALID, "sampler and envs differ in size or device");
+  if (!h->seeded) return fail(COG_ERR_NOT_RESET, "run() before reset()");
+  CK(cudaSetDevice(h->device));
+  if (s->stream != h->stream) CK(cudaStreamSynchronize(s->stream));
+  /* persistent grid: every SM filled once, warps walk the envs with a grid stride */
+  unsigned grid = blocks_for(h->n);
+  const unsigned resident = (unsigned)(h->sm_count * h->fused_blocks_per_sm);
+  if (grid > resident) grid = resident;
+  time_begin(h);
+  COG_LAUNCH(cog::k_step<true>, grid, cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm, h->n,
+             (const uint8_t *)nullptr, s->srng, s->actions, k_steps);
+  time_end(h);
+  g_launches++;
+  CK(cudaGetLastError());
+  return COG_OK;
+}
+
+int cog_vec_stats(cog_vec *h, uint64_t *out, size_t n) {
+  if (!h || !out || n > COG_STAT_COUNT) return fail(COG_ERR_INVALID, "bad argument");
+  unsigned long long tmp[COG_STAT_COUNT];
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpyAsync(tmp, h->B.stats, sizeof tmp, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  for (size_t i = 0; i < n; ++i) out[i] = tmp[i];
+  return COG_OK;
+}
+
+int cog_vec_stats_reset(cog_vec *h) {
+  if (!h) return fail(COG_ERR_INVALID, "NULL handle");
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemsetAsync(h->B.stats, 0, COG_STAT_COUNT * sizeof(unsigned long long), h->stream));
+  return COG_OK;
+}
+
+int cog_sync(cog_vec *h) {
+  if (!h) return fail(COG_ERR_INVALID, "NULL handle");
+  CK(cudaSetDevice(h->device));
+  return check_device_error(h);
+}
+
+int cog_vec_last_kernel_ms(cog_vec *h, float *ms) {
+  if (!h || !ms) return fail(COG_ERR_INVALID, "NULL argument");
+  if (!h->timed) return fail(COG_ERR_INVALID, "no kernel has been timed yet");
+  CK(cudaSetDevice(h->device));
+  CK(cudaEventSynchronize(h->ev1));
+  CK(cudaEventElapsedTime(ms, h->ev0, h->ev1));
+  return COG_OK;
+}
+
+}  /* extern "C" */

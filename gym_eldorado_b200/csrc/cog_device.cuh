@@ -1,0 +1,1124 @@
+/* cog_device.cuh — device-side game logic of the City of Gold hot path (sm_100a).
+ *
+ * Execution model: ONE WARP PER ENVIRONMENT.  Every branch of the game (phase,
+ * action kind, turn end, done) depends only on per-env values, so control flow is
+ * warp-uniform and the 32 lanes are used as a data-parallel axis:
+ *   lane l (1..21)  <-> card type l-1   (the five card piles, play/special/remove bits)
+ *   lane l (1..18)  <-> shop slot l-1   (stock, market flag, price)
+ *   lane d (0..6)   <-> hex direction d (neighbour cache, movement mask)
+ *   lane p (0..3)   <-> player p        (hidden per-player fields, P[p] masks)
+ * Mask index k of the reference's ActionMask is therefore bit k / lane k with no
+ * off-by-one shuffling, masks are bit sets built with __ballot_sync, and weighted
+ * draws from a pile are a warp prefix sum + ballot.
+ *
+ * The code restates the reference's semantics (file:line cited per function,
+ * paths relative to the reference tree); it shares no code with it.
+ */
+#ifndef COG_DEVICE_CUH
+#define COG_DEVICE_CUH
+#include <stdint.h>
+
+#include "cog_layout.h"
+#include "cog_tables.h"
+
+namespace cog {
+
+typedef uint8_t u8;
+typedef uint32_t u32;
+typedef uint64_t u64;
+#define COG_FULL 0xffffffffu
+
+/* ------------------------------------------------------------------ tables */
+struct card_def { u8 cost, market, single, res0, res1, res2, special; };
+struct piece_meta { u8 n_hexes, size, type, difficulty; };
+struct xy8 { int8_t x, y; };
+
+namespace tab {
+constexpr card_def CARDS[21] = COG_CARDS_INIT;
+constexpr u8 SLOT_CARD[18] = COG_SHOP_SLOT_CARD_INIT;
+
+/* per-lane constants, bit layout:
+ *  0-2 machete  3-5 paddle  6-8 coin  9 single_use  10-12 special  13-15 card cost
+ *  (card type lane-1);  16-18 price and 19 starts_in_market of shop slot lane-1 */
+constexpr u32 lane_const(int l) {
+  u32 v = 0;
+  if (l >= 1 && l <= 21) {
+    const card_def c = CARDS[l - 1];
+    v |= (u32)c.res0 | ((u32)c.res1 << 3) | ((u32)c.res2 << 6) | ((u32)c.single << 9) |
+         ((u32)c.special << 10) | ((u32)c.cost << 13);
+  }
+  if (l >= 1 && l <= 18) {
+    const card_def c = CARDS[SLOT_CARD[l - 1]];
+    v |= ((u32)c.cost << 16) | ((u32)c.market << 19);
+  }
+  return v;
+}
+constexpr u32 special_mask() { /* bit l: card l-1 has a special action (src/cards.cpp:311-323) */
+  u32 m = 0;
+  for (int c = 0; c < 21; ++c)
+    if (CARDS[c].special) m |= 1u << (c + 1);
+  return m;
+}
+}  // namespace tab
+
+#define COG_LC(l) tab::lane_const(l)
+__device__ const u32 LANE_CONST[32] = {
+    COG_LC(0),  COG_LC(1),  COG_LC(2),  COG_LC(3),  COG_LC(4),  COG_LC(5),  COG_LC(6),  COG_LC(7),
+    COG_LC(8),  COG_LC(9),  COG_LC(10), COG_LC(11), COG_LC(12), COG_LC(13), COG_LC(14), COG_LC(15),
+    COG_LC(16), COG_LC(17), COG_LC(18), COG_LC(19), COG_LC(20), COG_LC(21), COG_LC(22), COG_LC(23),
+    COG_LC(24), COG_LC(25), COG_LC(26), COG_LC(27), COG_LC(28), COG_LC(29), COG_LC(30), COG_LC(31)};
+constexpr u32 COG_SPECIAL_MASK = tab::special_mask();
+__device__ const u8 SLOT_CARD_D[18] = COG_SHOP_SLOT_CARD_INIT;
+
+/* piece geometry in half-hex units (src/map.cpp:446-462), hex codes and piece
+ * attributes (:464-695); encodings in tools/extract_tables.py */
+__device__ const xy8 COORDS_LARGE[37] = COG_COORDS_LARGE_INIT;
+__device__ const xy8 COORDS_SMALL[16] = COG_COORDS_SMALL_INIT;
+__device__ const xy8 COORDS_END[3] = COG_COORDS_END_INIT;
+__device__ const piece_meta PIECE_META[COG_N_PIECES_TOTAL] = COG_PIECE_META_INIT;
+__device__ const u8 PIECE_HEX[COG_N_PIECES_TOTAL][COG_PIECE_MAX_HEXES] = COG_PIECE_HEX_INIT;
+/* connection points per (host size, new size): MapPiece::get_ref_connection_points
+ * src/map.cpp:203-263.  kind 0 LARGE->LARGE, 1 LARGE->SMALL, 2 LARGE->TRIPLE, 3 SMALL->LARGE */
+__device__ const int8_t CONN_BASE[4][6][2] = {
+    {{8, 6}, {6, 8}, {0, 0}, {0, 0}, {0, 0}, {0, 0}},
+    {{3, 7}, {5, 5}, {7, 3}, {0, 0}, {0, 0}, {0, 0}},
+    {{0, 8}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}},
+    {{-7, 10}, {-5, 10}, {-3, 10}, {7, -10}, {5, -10}, {3, -10}}};
+
+enum { SIZE_LARGE = 0, SIZE_SMALL = 1, SIZE_TRIPLE = 2 };
+enum { TYPE_START = 0, TYPE_TRAVEL = 1, TYPE_END = 2 };
+enum { PH_INACTIVE = 0, PH_MOVEMENT = 1, PH_BUYING = 2, PH_MAX = 3 };
+enum { REQ_MACHETE = 0, REQ_PADDLE, REQ_COIN, REQ_DISCARD, REQ_REMOVE, REQ_NULL };
+enum { SP_NONE = 0, SP_TRANSMIT, SP_DRAW2, SP_DRAW3, SP_DRAW1_REMOVE1, SP_DRAW2_REMOVE2,
+       SP_NATIVE, SP_REMOVE_PENDING };
+enum { PFL_WON = 1, PFL_MIP = 2, PFL_CARD_FREE = 4, PFL_MOVE_FREE = 8 };
+
+/* hex code: bits 0-2 requirement+1 (0 = none), bits 3-5 n_required, bit 6 is_end */
+__device__ __forceinline__ int hex_req(u32 c) { return (c & 7) ? (int)(c & 7) - 1 : (int)REQ_NULL; }
+__device__ __forceinline__ int hex_n(u32 c) { return (int)((c >> 3) & 7); }
+__device__ __forceinline__ int hex_end(u32 c) { return (int)((c >> 6) & 1); }
+
+/* ----------------------------------------------------------- warp helpers */
+__device__ __forceinline__ u32 bcast(u32 v, int src) { return __shfl_sync(COG_FULL, v, src); }
+__device__ __forceinline__ u32 warp_incl_scan(u32 v, int lane) {
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    u32 t = __shfl_up_sync(COG_FULL, v, d);
+    if (lane >= d) v += t;
+  }
+  return v;
+}
+__device__ __forceinline__ u32 getb(u32 w, int p) { return (w >> (8 * p)) & 0xffu; }
+__device__ __forceinline__ u32 setb(u32 w, int p, u32 v) {
+  return (w & ~(0xffu << (8 * p))) | ((v & 0xffu) << (8 * p));
+}
+/* u8 arithmetic inside byte p (wraps like the reference's u_char counters) */
+__device__ __forceinline__ u32 addb(u32 w, int p, int d) { return setb(w, p, getb(w, p) + (u32)d); }
+__device__ __forceinline__ u32 setbit(u32 w, int b, bool v) {
+  return (w & ~(1u << b)) | ((u32)v << b);
+}
+
+/* -------------------------------------------------------------------- PRNG */
+/* std::default_random_engine = minstd_rand0: x <- 16807 x mod (2^31 - 1)
+ * (libstdc++ bits/random.h:1593); seed(): bits/random.tcc:119-126 */
+__host__ __device__ __forceinline__ u32 minstd_seed(u64 s) {
+  u64 x = s % 2147483647ull;
+  return (u32)(x ? x : 1);
+}
+__device__ __forceinline__ u32 minstd_next(u32 &s) {
+  u64 t = (u64)s * 16807ull; /* < 2^46: one Mersenne fold suffices */
+  u32 r = (u32)(t & 0x7fffffffu) + (u32)(t >> 31);
+  if (r >= 0x7fffffffu) r -= 0x7fffffffu;
+  s = r;
+  return r;
+}
+/* std::uniform_int_distribution<size_t>(0, n-1)(minstd_rand0): the "two divisions"
+ * downscaling branch of libstdc++ bits/uniform_int_dist.h:332-340 (the engine's
+ * range 2^31-3 is not 2^k-1, so Lemire's path is not taken).  A draw is consumed
+ * even for n == 1; rejection makes the count data dependent. */
+__device__ __forceinline__ u32 uniform_draw(u32 &s, u32 n) {
+  const u32 scaling = 2147483645u / n;
+  const u32 past = n * scaling;
+  u32 r;
+  do {
+    r = minstd_next(s) - 1u;
+  } while (r >= past);
+  return r / scaling;
+}
+
+/* one +60 degree step in half-hex axial coordinates: (x, y) -> (-y, x + y)
+ * (rotate_point src/map.cpp:17-37 through src/geometry.cpp:3-17; exact on the
+ * half lattice).  `times` keeps C remainder semantics like the reference. */
+__device__ __forceinline__ void rotate_pt(int &x, int &y, int times) {
+  int t = times % 6;
+  if (t < 0) t += 6;
+  for (int k = 0; k < t; ++k) {
+    int nx = -y, ny = x + y;
+    x = nx;
+    y = ny;
+  }
+}
+
+/* ------------------------------------------------------------ env in regs */
+/* parameters of vec_cog_env::reset(seed, ...) — identical for every env of a handle */
+struct Params {
+  u32 max_steps;
+  u32 n_players, n_pieces, difficulty;
+};
+
+/* device buffers of one handle */
+struct Buffers {
+  u32 *hidden;   /* [n][COG_HID_WORDS]  private state */
+  u8 *grid;      /* [n][48*48]          one hex code per cell, indexed like the map obs */
+  u8 *obs;       /* [n] ObsData */
+  u8 *masks;     /* [n] ActionMask  (selected_action_masks, "S") */
+  float *rewards;/* [n][4] */
+  u8 *dones;     /* [n] */
+  u8 *infos;     /* [n] Info */
+  u8 *agents;    /* [n] */
+  unsigned long long *stats; /* [COG_STAT_COUNT] */
+  int *err;      /* [0] first error code, [1] env index */
+};
+
+struct Env {
+  /* lane l <-> card type l-1; byte p = player p */
+  u32 draw, hand, active, played, discard;
+  u32 shop; /* lane l <-> slot l-1: bits 0-7 stock, bit 8 in_market */
+  u32 nbr;  /* lane d <-> direction d: byte p = hex code next to player p */
+  /* lane p <-> player p */
+  u32 pf, pc, pmv, ploc, Pplay, Pspec, Prem, Pms;
+  /* warp-uniform */
+  u32 rng, turn, agent, phase, n_in_market, info_steps;
+  u32 Splay, Sspec, Srem, Sms;
+  int res[3]; /* current_resources * 2 */
+  int minx, miny;
+};
+
+__device__ __forceinline__ int loc_x(u32 w) { return (int)(int16_t)(w & 0xffffu); }
+__device__ __forceinline__ int loc_y(u32 w) { return (int)(int16_t)(w >> 16); }
+__device__ __forceinline__ u32 loc_pack(int x, int y) {
+  return ((u32)x & 0xffffu) | ((u32)y << 16);
+}
+
+__device__ __forceinline__ void env_load(Env &E, const u32 *__restrict__ rec, int lane) {
+  E.draw = rec[COG_HL_DRAW * 32 + lane];
+  E.hand = rec[COG_HL_HAND * 32 + lane];
+  E.active = rec[COG_HL_ACTIVE * 32 + lane];
+  E.played = rec[COG_HL_PLAYED * 32 + lane];
+  E.discard = rec[COG_HL_DISCARD * 32 + lane];
+  E.shop = rec[COG_HL_SHOP * 32 + lane];
+  E.nbr = rec[COG_HL_NBR * 32 + lane];
+  const u32 pw = rec[COG_HL_PLAYER * 32 + lane];
+  const u32 ew = rec[COG_HL_ENV * 32 + lane];
+  const int q = lane & 3;
+  E.pf = bcast(pw, 4 * COG_PF_FLAGS + q);
+  E.pc = bcast(pw, 4 * COG_PF_COUNTS + q);
+  E.pmv = bcast(pw, 4 * COG_PF_MOVES + q);
+  E.ploc = bcast(pw, 4 * COG_PF_LOC + q);
+  E.Pplay = bcast(pw, 4 * COG_PF_MPLAY + q);
+  E.Pspec = bcast(pw, 4 * COG_PF_MSPEC + q);
+  E.Prem = bcast(pw, 4 * COG_PF_MREM + q);
+  E.Pms = bcast(pw, 4 * COG_PF_MMS + q);
+  E.rng = bcast(ew, COG_ES_RNG);
+  E.turn = bcast(ew, COG_ES_TURN);
+  const u32 misc = bcast(ew, COG_ES_MISC);
+  E.agent = misc & 0xffu;
+  E.phase = (misc >> 8) & 0xffu;
+  E.n_in_market = (misc >> 16) & 0xffu;
+  E.res[0] = (int)bcast(ew, COG_ES_RES0);
+  E.res[1] = (int)bcast(ew, COG_ES_RES1);
+  E.res[2] = (int)bcast(ew, COG_ES_RES2);
+  const u32 mn = bcast(ew, COG_ES_MIN);
+  E.minx = loc_x(mn);
+  E.miny = loc_y(mn);
+  E.Splay = bcast(ew, COG_ES_SPLAY);
+  E.Sspec = bcast(ew, COG_ES_SSPEC);
+  E.Srem = bcast(ew, COG_ES_SREM);
+  E.Sms = bcast(ew, COG_ES_SMS);
+  E.info_steps = bcast(ew, COG_ES_INFOSTEPS);
+}
+
+__device__ __forceinline__ void env_store(const Env &E, u32 *__restrict__ rec, int lane) {
+  rec[COG_HL_DRAW * 32 + lane] = E.draw;
+  rec[COG_HL_HAND * 32 + lane] = E.hand;
+  rec[COG_HL_ACTIVE * 32 + lane] = E.active;
+  rec[COG_HL_PLAYED * 32 + lane] = E.played;
+  rec[COG_HL_DISCARD * 32 + lane] = E.discard;
+  rec[COG_HL_SHOP * 32 + lane] = E.shop;
+  rec[COG_HL_NBR * 32 + lane] = E.nbr;
+  /* word 4 f + p <- field f of the lane that holds player p */
+  const int f = lane >> 2, q = lane & 3;
+  u32 pw = 0, t;
+  t = bcast(E.pf, q);    if (f == COG_PF_FLAGS) pw = t;
+  t = bcast(E.pc, q);    if (f == COG_PF_COUNTS) pw = t;
+  t = bcast(E.pmv, q);   if (f == COG_PF_MOVES) pw = t;
+  t = bcast(E.ploc, q);  if (f == COG_PF_LOC) pw = t;
+  t = bcast(E.Pplay, q); if (f == COG_PF_MPLAY) pw = t;
+  t = bcast(E.Pspec, q); if (f == COG_PF_MSPEC) pw = t;
+  t = bcast(E.Prem, q);  if (f == COG_PF_MREM) pw = t;
+  t = bcast(E.Pms, q);   if (f == COG_PF_MMS) pw = t;
+  rec[COG_HL_PLAYER * 32 + lane] = pw;
+  u32 ew = 0;
+  switch (lane) {
+  case COG_ES_RNG: ew = E.rng; break;
+  case COG_ES_TURN: ew = E.turn; break;
+  case COG_ES_MISC: ew = E.agent | (E.phase << 8) | (E.n_in_market << 16); break;
+  case COG_ES_RES0: ew = (u32)E.res[0]; break;
+  case COG_ES_RES1: ew = (u32)E.res[1]; break;
+  case COG_ES_RES2: ew = (u32)E.res[2]; break;
+  case COG_ES_MIN: ew = loc_pack(E.minx, E.miny); break;
+  case COG_ES_SPLAY: ew = E.Splay; break;
+  case COG_ES_SSPEC: ew = E.Sspec; break;
+  case COG_ES_SREM: ew = E.Srem; break;
+  case COG_ES_SMS: ew = E.Sms; break;
+  case COG_ES_INFOSTEPS: ew = E.info_steps; break;
+  default: break;
+  }
+  rec[COG_HL_ENV * 32 + lane] = ew;
+}
+
+/* ------------------------------------------------------------------ export */
+/* one ActionMask record (92 payload bytes of bool) from its four bit sets:
+ * lane w < 23 expands 4 mask bits into one 32-bit word -> one coalesced store */
+__device__ __forceinline__ void export_mask(u8 *dst, u32 play, u32 spec, u32 rem, u32 ms, int lane) {
+  const u64 lo = (u64)play | ((u64)spec << 22) | ((u64)rem << 44);
+  const u32 hi = (rem >> 20) | (ms << 2);
+  if (lane < 23) {
+    const u32 n = lane < 16 ? (u32)(lo >> (4 * lane)) & 15u : (hi >> (4 * (lane - 16))) & 15u;
+    reinterpret_cast<u32 *>(dst)[lane] = (n & 1u) | ((n & 2u) << 7) | ((n & 4u) << 14) | ((n & 8u) << 21);
+  }
+}
+
+/* everything a step can change in ObsData/ActionMask/agent_selection/Info, for
+ * the players in `pmask` (bit p): phase, resources, shop stock, DeckObs[p], P[p], S */
+__device__ __forceinline__ void export_dynamic(const Env &E, const Buffers &B, u64 i, u32 pmask, int lane) {
+  u8 *obs = B.obs + i * COGL_OBS_SIZE;
+  if (lane == 0) obs[COGL_OBS_PHASE] = (u8)E.phase;
+  if (lane < 3) reinterpret_cast<float *>(obs + COGL_OBS_RES)[lane] = 0.5f * (float)E.res[lane];
+  if (lane >= 1 && lane <= 18) obs[COGL_OBS_SHOP + lane - 1] = (u8)(E.shop & 0xffu);
+  for (int p = 0; p < 4; ++p) {
+    if (!((pmask >> p) & 1u)) continue;
+    u8 *pd = obs + COGL_OBS_PLAYER + COGL_PLAYER_STRIDE * p;
+    if (lane >= 1 && lane <= 21) {
+      pd[COGL_DK_DRAW + lane - 1] = (u8)getb(E.draw, p);
+      pd[COGL_DK_HAND + lane - 1] = (u8)getb(E.hand, p);
+      pd[COGL_DK_ACTIVE + lane - 1] = (u8)getb(E.active, p);
+      pd[COGL_DK_PLAYED + lane - 1] = (u8)getb(E.played, p);
+      pd[COGL_DK_DISCARD + lane - 1] = (u8)getb(E.discard, p);
+    }
+    export_mask(pd + COGL_PD_MASK, bcast(E.Pplay, p), bcast(E.Pspec, p), bcast(E.Prem, p),
+                bcast(E.Pms, p), lane);
+  }
+  export_mask(B.masks + i * COGL_MASK_SIZE, E.Splay, E.Sspec, E.Srem, E.Sms, lane);
+  if (lane == 0) B.agents[i] = (u8)E.agent;
+  if (lane < 4)
+    B.infos[i * COGL_INFO_SIZE + COGL_INFO_AGENT + COGL_INFO_AGENT_STRIDE * lane] =
+        (u8)getb(E.info_steps, lane);
+}
+
+/* ------------------------------------------------------------------- decks */
+__device__ __forceinline__ int res_get(const Env &E, int k) {
+  return k == 0 ? E.res[0] : (k == 1 ? E.res[1] : E.res[2]);
+}
+__device__ __forceinline__ void res_clear(Env &E) { E.res[0] = E.res[1] = E.res[2] = 0; }
+__device__ __forceinline__ void res_set(Env &E, int k, int v) {
+  if (k == 0) E.res[0] = v;
+  else if (k == 1) E.res[1] = v;
+  else E.res[2] = v;
+}
+
+/* weighted pick without replacement: the card whose cumulative count first exceeds
+ * `target` (the `while (target >= pile[card])` scans of src/cards.cpp:192-197,
+ * src/player.cpp:94-99,117-122) as a warp prefix sum + ballot.  Returns the lane
+ * (= card type + 1) or 0 when target is beyond the pile (UB in the reference). */
+__device__ __forceinline__ int pile_pick(u32 pile, int p, u32 target, int lane) {
+  const u32 incl = warp_incl_scan(getb(pile, p), lane);
+  const u32 hit = __ballot_sync(COG_FULL, incl > target);
+  return hit ? __ffs((int)hit) - 1 : 0;
+}
+
+/* Deck::draw src/cards.cpp:183-211 (with move_discard_to_draw :234-240).
+ * `pc` = the player's COG_PF_COUNTS word (uniform copy, updated in place). */
+__device__ __forceinline__ void deck_draw(Env &E, u32 &pc, int p, u32 n, int lane) {
+  u32 n_in_draw = getb(pc, 2);
+  if (n_in_draw < n) {
+    const u32 d = getb(E.discard, p);
+    E.draw = addb(E.draw, p, (int)d);
+    E.discard = setb(E.discard, p, 0);
+    n_in_draw = (n_in_draw + __reduce_add_sync(COG_FULL, d)) & 0xffu;
+  }
+  if (n_in_draw < n) n = n_in_draw;
+  for (u32 i = 0; i < n; ++i) {
+    const u32 target = uniform_draw(E.rng, n_in_draw);
+    const int cl = pile_pick(E.draw, p, target, lane);
+    if (cl) {
+      if (lane == cl) {
+        E.draw = addb(E.draw, p, -1);
+        E.hand = addb(E.hand, p, 1);
+      }
+      E.Splay |= 1u << cl;
+      E.Sspec = (E.Sspec & ~(1u << cl)) | (COG_SPECIAL_MASK & (1u << cl));
+    }
+    n_in_draw = (n_in_draw - 1) & 0xffu;
+  }
+  pc = setb(pc, 2, n_in_draw);
+  pc = setb(pc, 0, getb(pc, 0) + n);
+}
+
+/* hand -> active; Deck::activate src/cards.cpp:242-253 */
+__device__ __forceinline__ void deck_activate(Env &E, u32 &pc, int p, int idx, int lane) {
+  const int cl = idx + 1;
+  pc = setb(pc, 0, getb(pc, 0) - 1);
+  pc = setb(pc, 1, getb(pc, 1) + 1);
+  pc = setb(pc, 3, (u32)idx);
+  const u32 prev = bcast(getb(E.hand, p), cl);
+  if (lane == cl) {
+    E.hand = addb(E.hand, p, -1);
+    E.active = addb(E.active, p, 1);
+  }
+  const bool still = prev > 1;
+  E.Splay = setbit(E.Splay, cl, still);
+  E.Sspec = setbit(E.Sspec, cl, still && ((COG_SPECIAL_MASK >> cl) & 1u));
+}
+/* Deck::play_last_activated src/cards.cpp:255-261 */
+__device__ __forceinline__ void deck_play_last_activated(Env &E, u32 &pc, int p, int lane) {
+  const int cl = (int)getb(pc, 3) + 1;
+  pc = setb(pc, 1, getb(pc, 1) - 1);
+  if (lane == cl) {
+    E.active = addb(E.active, p, -1);
+    if (!((LANE_CONST[lane] >> 9) & 1u)) E.played = addb(E.played, p, 1);
+  }
+}
+/* Deck::play_immediate src/cards.cpp:263-273 */
+__device__ __forceinline__ void deck_play_immediate(Env &E, u32 &pc, int p, int idx, int lane) {
+  const int cl = idx + 1;
+  pc = setb(pc, 0, getb(pc, 0) - 1);
+  const u32 prev = bcast(getb(E.hand, p), cl);
+  if (lane == cl) {
+    E.hand = addb(E.hand, p, -1);
+    E.played = addb(E.played, p, 1);
+  }
+  const bool still = prev > 1;
+  E.Splay = setbit(E.Splay, cl, still);
+  E.Sspec = setbit(E.Sspec, cl, still && ((COG_SPECIAL_MASK >> cl) & 1u));
+}
+/* Deck::remove_immediate src/cards.cpp:281-290 */
+__device__ __forceinline__ void deck_remove_immediate(Env &E, u32 &pc, int p, int idx, int lane) {
+  const int cl = idx + 1;
+  pc = setb(pc, 0, getb(pc, 0) - 1);
+  const u32 prev = bcast(getb(E.hand, p), cl);
+  if (lane == cl) E.hand = addb(E.hand, p, -1);
+  const bool still = prev > 1;
+  E.Srem = setbit(E.Srem, cl, ((E.Srem >> cl) & 1u) && still);
+  const bool play = ((E.Splay >> cl) & 1u) && still;
+  E.Splay = setbit(E.Splay, cl, play);
+  E.Sspec = setbit(E.Sspec, cl, play && ((COG_SPECIAL_MASK >> cl) & 1u));
+}
+
+/* ------------------------------------------------------------------ player */
+/* Player::disable_playing src/player.cpp:191-196 */
+__device__ __forceinline__ void player_disable_playing(Env &E) {
+  E.Splay = 1u;
+  E.Sspec = 1u;
+}
+/* Player::enable_playing src/player.cpp:198-206: play[k] = hand[k-1] > 0 is one ballot */
+__device__ __forceinline__ void player_enable_playing(Env &E, int p, int lane) {
+  E.Srem = 1u;
+  const u32 have = __ballot_sync(COG_FULL, lane >= 1 && lane <= 21 && getb(E.hand, p) > 0);
+  E.Splay = (E.Splay & 1u) | have;
+  E.Sspec = (E.Sspec & 1u) | (have & COG_SPECIAL_MASK);
+}
+/* Player::discard_cards src/player.cpp:85-104 (no clamp) / remove_cards :106-131 (clamped) */
+__device__ __forceinline__ void player_drop_active(Env &E, u32 &pc, int p, u32 n, bool remove, int lane) {
+  const u32 n_act = getb(pc, 1);
+  if (remove && n > n_act) n = n_act;
+  for (u32 i = 0; i < n; ++i) {
+    if (n_act <= i) break; /* the reference would draw from an empty range (UB) */
+    const u32 target = uniform_draw(E.rng, n_act - i);
+    const int cl = pile_pick(E.active, p, target, lane);
+    pc = setb(pc, 1, getb(pc, 1) - 1);
+    if (cl && lane == cl) {
+      E.active = addb(E.active, p, -1);
+      if (!remove) E.discard = addb(E.discard, p, 1);
+    }
+  }
+}
+/* Player::handle_requirement src/player.cpp:141-162 */
+__device__ __forceinline__ void player_handle_requirement(Env &E, u32 &pf, u32 &pc, int p, int req,
+                                                          u32 n, int lane) {
+  if (req < 3) {
+    const int left = res_get(E, req) - 2 * (int)n;
+    res_clear(E);
+    res_set(E, req, left);
+    if (!(pf & PFL_MIP)) {
+      deck_play_last_activated(E, pc, p, lane);
+      pf |= PFL_MIP;
+    }
+  } else if (req == REQ_REMOVE) {
+    player_drop_active(E, pc, p, n, true, lane);
+    res_clear(E);
+    pf &= ~(u32)PFL_MIP;
+  } else if (req == REQ_DISCARD) {
+    player_drop_active(E, pc, p, n, false, lane);
+    res_clear(E);
+    pf &= ~(u32)PFL_MIP;
+  }
+}
+/* Player::end_turn src/player.cpp:170-180 (+ Deck::discard_all_active/_played
+ * src/cards.cpp:219-232); P[p] = S is save_actionmask :166 */
+__device__ __forceinline__ void player_end_turn(Env &E, u32 &pc, int p, int lane) {
+  pc = setb(pc, 1, 0);
+  E.discard = addb(E.discard, p, (int)(getb(E.active, p) + getb(E.played, p)));
+  E.active = setb(E.active, p, 0);
+  E.played = setb(E.played, p, 0);
+  const int n_draw = 4 - (int)getb(pc, 0);
+  if (n_draw > 0) deck_draw(E, pc, p, (u32)n_draw, lane);
+  res_clear(E);
+  if (lane == p) {
+    E.Pplay = E.Splay;
+    E.Pspec = E.Sspec;
+    E.Prem = E.Srem;
+    E.Pms = E.Sms;
+  }
+}
+
+/* -------------------------------------------------------------------- shop */
+/* Shop::get src/cards.cpp:136-142; returns the card type */
+__device__ __forceinline__ int shop_get(Env &E, int idx, int lane) {
+  const int sl = idx + 1;
+  const u32 w = bcast(E.shop, sl);
+  const u32 stock = ((w & 0xffu) - 1u) & 0xffu;
+  u32 inm = (w >> 8) & 1u;
+  if (!stock && inm) {
+    inm = 0;
+    E.n_in_market = (E.n_in_market - 1u) & 0xffu;
+  }
+  if (lane == sl) E.shop = stock | (inm << 8);
+  return idx < 18 ? (int)SLOT_CARD_D[idx] : 0;
+}
+/* Shop::buy src/cards.cpp:102-106 */
+__device__ __forceinline__ int shop_buy(Env &E, int idx, int lane) {
+  const int sl = idx + 1;
+  const u32 inm = (bcast(E.shop, sl) >> 8) & 1u;
+  E.n_in_market = (E.n_in_market + 1u - inm) & 0xffu;
+  if (lane == sl) E.shop |= 0x100u;
+  return shop_get(E, idx, lane);
+}
+/* Shop::set_available_mask src/cards.cpp:109-121: bits 1..18 of get_from_shop.
+ * coin2 = coins * 2; the comparison is strict (coins > cost). */
+__device__ __forceinline__ u32 shop_available_bits(const Env &E, int coin2, int lane) {
+  const int cost = (int)((LANE_CONST[lane] >> 16) & 7u);
+  const bool open = E.n_in_market < 6 ? (E.shop & 0xffu) > 0 : ((E.shop >> 8) & 1u) != 0;
+  return __ballot_sync(COG_FULL, lane >= 1 && lane <= 18 && open && coin2 > 2 * cost);
+}
+/* Shop::set_transmit_mask src/cards.cpp:123-127 */
+__device__ __forceinline__ u32 shop_transmit_bits(const Env &E, int lane) {
+  return __ballot_sync(COG_FULL, lane >= 1 && lane <= 18 && (E.shop & 0xffu) > 0);
+}
+
+/* --------------------------------------------------------------------- map */
+/* Map::get_from_array src/map.cpp:273-275 on the one-byte-per-hex grid: the
+ * reference truncates (coord - min) toward zero, then adds 1 (SURVEY A#17) */
+__device__ __forceinline__ u32 grid_lookup(const u8 *__restrict__ grid, int x, int y, int minx, int miny) {
+  const int ix = (x - minx) / 2 + 1;
+  const int iy = (y - miny) / 2 + 1;
+  if (ix < 0 || iy < 0 || ix >= COGL_GRID || iy >= COGL_GRID) return 0;
+  return grid[ix * COGL_GRID + iy];
+}
+__device__ __forceinline__ void dir_delta(int d, int &dx, int &dy) {
+  /* include/geometry.h:42-50: none, E, NE, NW, W, SW, SE (x2) */
+  dx = d == 1 ? 2 : (d == 3 || d == 4) ? -2 : d == 6 ? 2 : 0;
+  dy = d == 2 ? 2 : d == 3 ? 2 : (d == 5 || d == 6) ? -2 : 0;
+}
+/* refresh the neighbour cache of player p from the grid (lanes 0..6) */
+__device__ __forceinline__ void nbr_refresh(Env &E, const u8 *__restrict__ grid, int p, int lane) {
+  const u32 loc = bcast(E.ploc, p);
+  int dx, dy;
+  dir_delta(lane, dx, dy);
+  u32 code = 0;
+  if (lane < 7) code = grid_lookup(grid, loc_x(loc) + dx, loc_y(loc) + dy, E.minx, E.miny);
+  E.nbr = setb(E.nbr, p, code);
+}
+/* Map::set_movement_mask src/map.cpp:369-387: bits 1..6 of move for `player`,
+ * with explicit resources (x2) and active-card count */
+__device__ __forceinline__ u32 movement_bits(const Env &E, int player, int r0, int r1, int r2,
+                                             int n_active, int lane) {
+  const u32 c = getb(E.nbr, player);
+  const int req = hex_req(c), n = hex_n(c);
+  bool filled;
+  if (req >= REQ_DISCARD) filled = n_active > n;
+  else filled = (req == 0 ? r0 : (req == 1 ? r1 : r2)) >= 2 * n;
+  return __ballot_sync(COG_FULL, lane >= 1 && lane <= 6 && req != REQ_NULL && filled);
+}
+
+/* ----------------------------------------------------------------- cog_env */
+/* cog_env::update_observation src/environment.cpp:252-279 */
+__device__ __forceinline__ void env_update_observation(Env &E, int agent, int lane) {
+  u32 move = 1u, shop = 1u;
+  if (E.phase == PH_MOVEMENT) {
+    const int n_active = (int)getb(bcast(E.pc, agent), 1);
+    move |= movement_bits(E, agent, E.res[0], E.res[1], E.res[2], n_active, lane);
+  } else if (E.phase == PH_BUYING) {
+    shop |= shop_available_bits(E, E.res[2], lane);
+  }
+  if (lane == agent) E.Pms = move | (shop << 7);
+}
+__device__ __forceinline__ void env_cycle_phase(Env &E) { /* include/player.h:78-84 */
+  u32 n = E.phase + 1;
+  if (n >= PH_MAX) n -= PH_MAX;
+  E.phase = n;
+}
+
+/* --------------------------------------------------------- board generation */
+/* Per-warp scratch in shared memory.  The occupancy bitmap is a 128 x 128 torus of
+ * half-hex cells: a board that fits the 48 x 48 observation spans <= 94 half units,
+ * and a candidate footprint reaches < 17 further, so two distinct live cells can
+ * never alias (boards that outgrow the observation are reported immediately). */
+enum { BG_OCC_WORDS = 128 * 128 / 32, BG_MAX_PLACED = 32 };
+struct bg_pose { int16_t cx, cy, rot, pad; };
+struct bg_placed { int16_t cx, cy, rot; u8 piece, pad; };
+struct BoardScratch {
+  u32 occ[BG_OCC_WORDS];
+  bg_pose pose[COG_N_PIECES_TOTAL];  /* current pose of each piece (global objects in the reference) */
+  bg_placed placed[BG_MAX_PLACED];   /* Map::pieces, with the pose each entry was placed at */
+};
+struct BoardState {
+  int n_list;
+  int minx, miny, maxx, maxy; /* Map::min_xy / max_xy */
+};
+
+__device__ __forceinline__ const xy8 *piece_coords(int size) {
+  return size == SIZE_LARGE ? COORDS_LARGE : (size == SIZE_SMALL ? COORDS_SMALL : COORDS_END);
+}
+__device__ __forceinline__ u32 occ_index(int x, int y) { return ((u32)(x & 127) << 7) | (u32)(y & 127); }
+
+/* Map::reset src/map.cpp:744-752 */
+__device__ __forceinline__ void bg_map_reset(BoardScratch &sc, BoardState &st, int lane) {
+  for (int w = lane; w < BG_OCC_WORDS; w += 32) sc.occ[w] = 0;
+  st.n_list = 0;
+  st.minx = st.miny = st.maxx = st.maxy = 0;
+  __syncwarp();
+}
+
+/* Map::add_piece src/map.cpp:309-341 with MapPiece::rotate/translate :179-191.
+ * Lanes place the piece's hexes in parallel.  Returns 0 or COG error (-3). */
+__device__ __forceinline__ int bg_add_piece(BoardScratch &sc, BoardState &st, int piece, int px, int py,
+                                            int rotation, int lane) {
+  const int r = rotation % 6;
+  if (st.n_list >= BG_MAX_PLACED) return -3;
+  const int rot = sc.pose[piece].rot + r, cx = sc.pose[piece].cx + px, cy = sc.pose[piece].cy + py;
+  __syncwarp();
+  if (lane == 0) {
+    sc.pose[piece].rot = (int16_t)rot;
+    sc.pose[piece].cx = (int16_t)cx;
+    sc.pose[piece].cy = (int16_t)cy;
+    bg_placed pl;
+    pl.cx = (int16_t)cx; pl.cy = (int16_t)cy; pl.rot = (int16_t)rot; pl.piece = (u8)piece; pl.pad = 0;
+    sc.placed[st.n_list] = pl;
+  }
+  st.n_list++;
+  const piece_meta pm = PIECE_META[piece];
+  const xy8 *co = piece_coords(pm.size);
+  int lminx = st.minx, lminy = st.miny, lmaxx = st.maxx, lmaxy = st.maxy;
+  for (int h = lane; h < pm.n_hexes; h += 32) {
+    int x = co[h].x, y = co[h].y;
+    rotate_pt(x, y, rot);
+    x += cx;
+    y += cy;
+    const u32 b = occ_index(x, y);
+    atomicOr(&sc.occ[b >> 5], 1u << (b & 31));
+    lminx = min(lminx, x); lmaxx = max(lmaxx, x);
+    lminy = min(lminy, y); lmaxy = max(lmaxy, y);
+  }
+  st.minx = __reduce_min_sync(COG_FULL, lminx);
+  st.miny = __reduce_min_sync(COG_FULL, lminy);
+  st.maxx = __reduce_max_sync(COG_FULL, lmaxx);
+  st.maxy = __reduce_max_sync(COG_FULL, lmaxy);
+  __syncwarp();
+  /* largest cell index (coord - min + 2) / 2 must stay inside the 48 x 48 observation */
+  if ((st.maxx - st.minx + 2) / 2 > COGL_GRID - 1 || (st.maxy - st.miny + 2) / 2 > COGL_GRID - 1) return -3;
+  return 0;
+}
+
+/* which connection table applies (MapPiece::get_ref_connection_points src/map.cpp:203-263):
+ * returns the number of entries of host->get_centered_connections(new) (0 = none) */
+__device__ __forceinline__ int bg_conn_kind(int host, int newp, int &kind, int &n_alt, int &first_opt,
+                                            int &n_opts) {
+  const piece_meta h = PIECE_META[host], n = PIECE_META[newp];
+  kind = -1;
+  if (h.size == SIZE_LARGE) {
+    if (n.size == SIZE_LARGE) { kind = 0; n_alt = 2; first_opt = -2; n_opts = 6; }
+    else if (n.size == SIZE_SMALL) { kind = 1; n_alt = 3; first_opt = -1; n_opts = 2; }
+    else if (n.size == SIZE_TRIPLE && h.type != TYPE_START) { kind = 2; n_alt = 1; first_opt = -3; n_opts = 1; }
+  } else if (h.size == SIZE_SMALL && n.size == SIZE_LARGE) {
+    kind = 3; n_alt = 6; first_opt = -2; n_opts = 6;
+  }
+  if (kind < 0) return 0;
+  return kind == 3 ? n_alt : 7 * n_alt; /* base entries plus six rotated copies :249-260 */
+}
+/* rotation option `k` of a connection kind (:203-263): {-2..3}, {-1,2}, {-3} */
+__device__ __forceinline__ int bg_rot_option(int kind, int k) {
+  return kind == 1 ? (k == 0 ? -1 : 2) : (kind == 2 ? -3 : k - 2);
+}
+/* entry e of host->get_centered_connections(new) (src/map.cpp:192-201) */
+__device__ __forceinline__ void bg_conn_entry(const BoardScratch &sc, int host, int kind, int n_alt, int e,
+                                              int &x, int &y, int &rot_add) {
+  const int i = e / n_alt, j = e - i * n_alt;
+  const bg_pose hp = sc.pose[host];
+  x = CONN_BASE[kind][j][0];
+  y = CONN_BASE[kind][j][1];
+  rotate_pt(x, y, i);
+  rotate_pt(x, y, hp.rot);
+  x += hp.cx;
+  y += hp.cy;
+  rot_add = i + hp.rot;
+}
+
+/* Map::add_random_piece src/map.cpp:277-307 (+ overlap :53-74).  One round per host
+ * piece; the lanes test that host's <= 21 connection entries in parallel against the
+ * occupancy bitmap.  Returns 1 placed, 0 no candidate fits, < 0 error. */
+__device__ __forceinline__ int bg_add_random_piece(BoardScratch &sc, BoardState &st, int piece, u32 &rng,
+                                                   int lane) {
+  __syncwarp();
+  if (lane == 0) { /* MapPiece::reset :174-177 acts on the shared piece object */
+    sc.pose[piece].cx = 0; sc.pose[piece].cy = 0; sc.pose[piece].rot = 0;
+  }
+  __syncwarp();
+  const piece_meta pm = PIECE_META[piece];
+  const xy8 *co = piece_coords(pm.size);
+  u32 my_valid = 0; /* lane k keeps the valid-entry bit set of host k */
+  int n_valid = 0;
+  for (int k = 0; k < st.n_list; ++k) {
+    const int host = sc.placed[k].piece;
+    int kind, n_alt = 1, first_opt = 0, n_opts = 0;
+    const int n_ent = bg_conn_kind(host, piece, kind, n_alt, first_opt, n_opts);
+    bool ok = false;
+    if (lane < n_ent) {
+      int x, y, rot_add;
+      bg_conn_entry(sc, host, kind, n_alt, lane, x, y, rot_add);
+      const int r0 = first_opt + rot_add; /* only the FIRST rotation option is tested */
+      ok = true;
+      for (int h = 0; h < pm.n_hexes; ++h) {
+        int hx = co[h].x, hy = co[h].y;
+        rotate_pt(hx, hy, r0);
+        const u32 b = occ_index(hx + x, hy + y);
+        if ((sc.occ[b >> 5] >> (b & 31)) & 1u) { ok = false; break; }
+      }
+    }
+    const u32 vm = __ballot_sync(COG_FULL, ok);
+    if (lane == k) my_valid = vm;
+    n_valid += __popc(vm);
+  }
+  if (!n_valid) return 0;
+  const u32 idx = uniform_draw(rng, (u32)n_valid);
+  const u32 cnt = (u32)__popc(my_valid);
+  const u32 incl = warp_incl_scan(cnt, lane);
+  const u32 hit = __ballot_sync(COG_FULL, incl > idx);
+  const int k = __ffs((int)hit) - 1;
+  const u32 vm = bcast(my_valid, k);
+  const u32 within = idx - (bcast(incl, k) - bcast(cnt, k));
+  const int e = (int)__fns(vm, 0, (int)within + 1);
+  const int host = sc.placed[k].piece;
+  int kind, n_alt = 1, first_opt = 0, n_opts = 1;
+  bg_conn_kind(host, piece, kind, n_alt, first_opt, n_opts);
+  int x, y, rot_add;
+  bg_conn_entry(sc, host, kind, n_alt, e, x, y, rot_add);
+  const int rot_idx = (int)uniform_draw(rng, (u32)n_opts);
+  const int rc = bg_add_piece(sc, st, piece, x, y, bg_rot_option(kind, rot_idx) + rot_add, lane);
+  return rc ? rc : 1;
+}
+
+/* Map::generate src/map.cpp:697-742.  The reference recurses (rng BY VALUE, no map
+ * reset in the travel-piece branch); here the <= 5 frames live on an explicit stack.
+ * Returns 0, -2 (generate_map_failure) or -3 (board outgrew the observation). */
+__device__ __forceinline__ int bg_generate(BoardScratch &sc, BoardState &st, u32 rng0, int n_pieces,
+                                           int difficulty, int lane) {
+  enum { F_ENTER = 0, F_LOOP = 1, F_DONE = 2, MAX_DEPTH = 5 };
+  u32 f_rng[MAX_DEPTH];
+  u64 f_valid[MAX_DEPTH]; /* valid_indices as a list of nibbles */
+  int f_nvalid[MAX_DEPTH], f_i[MAX_DEPTH], f_state[MAX_DEPTH];
+  int depth = 0;
+  f_rng[0] = rng0;
+  f_state[0] = F_ENTER;
+  if (lane < 2) { /* the start pieces are never moved */
+    sc.pose[lane].cx = 0; sc.pose[lane].cy = 0; sc.pose[lane].rot = 0;
+  }
+  __syncwarp();
+  for (;;) {
+    if (f_state[depth] == F_ENTER) {
+      const int start = (int)uniform_draw(f_rng[depth], 2);
+      const int rc = bg_add_piece(sc, st, start, 0, 0, 0, lane);
+      if (rc) return rc;
+      u64 v = 0;
+      int nv = 0;
+      for (int i = 0; i < 16; ++i)
+        if ((int)PIECE_META[2 + i].difficulty <= difficulty) v |= (u64)i << (4 * nv++);
+      f_valid[depth] = v;
+      f_nvalid[depth] = nv;
+      f_i[depth] = 0;
+      f_state[depth] = F_LOOP;
+    } else if (f_state[depth] == F_LOOP) {
+      bool descend = false;
+      if (f_i[depth] < n_pieces) {
+        int success = 0, next_idx = 0;
+        if (f_nvalid[depth]) {
+          const u32 pos = uniform_draw(f_rng[depth], (u32)f_nvalid[depth]);
+          next_idx = (int)((f_valid[depth] >> (4 * pos)) & 15u);
+          success = bg_add_random_piece(sc, st, 2 + next_idx, f_rng[depth], lane);
+          if (success < 0) return success;
+        }
+        f_i[depth]++;
+        if (success) {
+          /* valid_indices.erase(begin + next_idx): the piece index is used as a POSITION;
+           * past-the-end degenerates to pop_back (libstdc++ bits/vector.tcc:182-190) */
+          const int nv = f_nvalid[depth];
+          if (next_idx < nv - 1) {
+            const u64 v = f_valid[depth];
+            const u64 low = v & ((1ull << (4 * next_idx)) - 1ull);
+            f_valid[depth] = low | ((v >> (4 * (next_idx + 1))) << (4 * next_idx));
+          }
+          f_nvalid[depth] = nv - 1;
+        } else {
+          descend = true; /* generate(..., failures + 1, rng) WITHOUT reset, then carry on */
+        }
+      } else {
+        const int endp = 18 + (int)uniform_draw(f_rng[depth], 2);
+        const int ok = bg_add_random_piece(sc, st, endp, f_rng[depth], lane);
+        if (ok < 0) return ok;
+        f_state[depth] = F_DONE;
+        if (!ok) {
+          bg_map_reset(sc, st, lane);
+          descend = true;
+        }
+      }
+      if (descend) {
+        if (depth + 1 >= MAX_DEPTH) return -2; /* failures >= MAX_FAILURES throws */
+        f_rng[depth + 1] = f_rng[depth];
+        f_state[depth + 1] = F_ENTER;
+        depth++;
+      }
+    } else {
+      if (depth == 0) return 0;
+      depth--;
+    }
+  }
+}
+
+/* Map::finalize src/map.cpp:389-405 (cell index from the last add_piece :335-340).
+ * (1) scatter one code per hex into the private 48 x 48 grid (pieces in placement
+ * order, so later pieces win index collisions like the reference's overwrite);
+ * (2) encode the 48 x 48 x 7 observation from the grid with 16-byte coalesced stores:
+ * feature 1+requirement = n_required, feature 6 = is_end, feature 0 never written. */
+__device__ __forceinline__ int bg_finalize(const BoardScratch &sc, const BoardState &st, u8 *grid,
+                                           u8 *mapobs, int lane) {
+  uint4 *g4 = reinterpret_cast<uint4 *>(grid);
+  for (int w = lane; w < COGL_GRID_BYTES / 16; w += 32) g4[w] = make_uint4(0, 0, 0, 0);
+  __syncwarp();
+  bool bad = false;
+  for (int k = 0; k < st.n_list; ++k) {
+    const bg_placed pl = sc.placed[k];
+    const piece_meta pm = PIECE_META[pl.piece];
+    const xy8 *co = piece_coords(pm.size);
+    for (int h = lane; h < pm.n_hexes; h += 32) {
+      int x = co[h].x, y = co[h].y;
+      rotate_pt(x, y, pl.rot);
+      const int ix = (x + pl.cx - st.minx + 2) / 2, iy = (y + pl.cy - st.miny + 2) / 2;
+      if (ix >= COGL_GRID || iy >= COGL_GRID) bad = true;
+      else grid[ix * COGL_GRID + iy] = PIECE_HEX[pl.piece][h];
+    }
+    __syncwarp();
+  }
+  if (__any_sync(COG_FULL, bad)) return -3;
+  uint4 *m4 = reinterpret_cast<uint4 *>(mapobs);
+  for (int c = lane; c < COGL_MAP_BYTES / 16; c += 32) {
+    const int o = 16 * c, cell0 = o / 7;
+    u32 w[4] = {0, 0, 0, 0};
+    u32 codes = 0; /* the <= 4 cells this chunk touches */
+    for (int j = 0; j < 4; ++j)
+      if (cell0 + j < COGL_GRID_BYTES) codes |= (u32)grid[cell0 + j] << (8 * j);
+    if (codes) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int cell = (o + j) / 7, f = (o + j) - 7 * cell;
+        const u32 code = (codes >> (8 * (cell - cell0))) & 0xffu;
+        u32 v = 0;
+        if (f == 6) v = (u32)hex_end(code);
+        else if (f >= 1 && hex_req(code) == f - 1) v = (u32)hex_n(code);
+        w[j >> 2] |= v << (8 * (j & 3));
+      }
+    }
+    m4[c] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------- reset */
+__device__ __forceinline__ void report_error(const Buffers &B, int code, u64 i, int lane) {
+  if (lane == 0 && atomicCAS(&B.err[0], 0, code) == 0) B.err[1] = (int)i;
+}
+
+/* Player::reset src/player.cpp:29-43 -> Deck::reset src/cards.cpp:163-171.
+ * ActionMask::reset (include/api.h:104-118) leaves move[1..]/get_from_shop[1..] alone;
+ * DeckObs::reset (:75-81) leaves `played` alone; idx_last_activated survives. */
+__device__ __forceinline__ void player_reset(Env &E, int p, int lane) {
+  u32 pc = bcast(E.pc, p) & 0xff000000u; /* n_in_hand = n_active = n_in_draw = 0 */
+  E.draw = setb(E.draw, p, 0);
+  E.hand = setb(E.hand, p, 0);
+  E.active = setb(E.active, p, 0);
+  E.discard = setb(E.discard, p, lane == 1 ? 3u : lane == 8 ? 4u : lane == 6 ? 1u : 0u);
+  E.Splay = 1u; E.Srem = 1u; E.Sspec = 1u;
+  E.Sms |= 1u | (1u << 7);
+  deck_draw(E, pc, p, 4, lane);
+  if (lane == p) {
+    E.pf = 0; E.pmv = 0; E.pc = pc;
+    E.Pplay = E.Splay; E.Pspec = E.Sspec; E.Prem = E.Srem; E.Pms = E.Sms; /* save_actionmask */
+  }
+}
+
+/* cog_env::reset() src/environment.cpp:42-64.  The board comes from a COPY of the
+ * env RNG (:48), so the deck draws that follow replay the same stream prefix.
+ * Returns 0 or the error that was reported. */
+__device__ __forceinline__ int env_reset(Env &E, const Params &prm, const Buffers &B, u64 i,
+                                         BoardScratch &sc, int lane) {
+  E.agent = 0;
+  E.phase = PH_INACTIVE;
+  BoardState st;
+  bg_map_reset(sc, st, lane);
+  int rc = bg_generate(sc, st, E.rng, (int)prm.n_pieces, (int)prm.difficulty, lane);
+  u8 *grid = B.grid + i * COGL_GRID_BYTES;
+  if (!rc) rc = bg_finalize(sc, st, grid, B.obs + i * COGL_OBS_SIZE, lane);
+  if (rc) {
+    report_error(B, rc, i, lane);
+    return rc;
+  }
+  __syncwarp();
+  E.minx = st.minx;
+  E.miny = st.miny;
+  const int np = (int)prm.n_players < 4 ? (int)prm.n_players : 4;
+  for (int p = 0; p < np; ++p) player_reset(E, p, lane);
+  /* Map::add_players src/map.cpp:343-354: player i stands on hex i of the start piece
+   * (defined like that for fewer than 4 players too; SURVEY A#13) */
+  if (lane < np) E.ploc = loc_pack(COORDS_LARGE[lane].x, COORDS_LARGE[lane].y);
+  for (int p = 0; p < np; ++p) nbr_refresh(E, grid, p, lane);
+  /* Shop::reset src/cards.cpp:94-100 (n_in_market is NOT reset) */
+  E.shop = (lane >= 1 && lane <= 18) ? (3u | (((LANE_CONST[lane] >> 19) & 1u) << 8)) : 0u;
+  E.turn = 0;
+  for (int p = 0; p < np; ++p) env_update_observation(E, p, lane);
+  E.Splay = bcast(E.Pplay, 0); /* load_actionmask of agent 0 :62-63 */
+  E.Sspec = bcast(E.Pspec, 0);
+  E.Srem = bcast(E.Prem, 0);
+  E.Sms = bcast(E.Pms, 0);
+  if (lane == 0) atomicAdd(&B.stats[10 /* COG_STAT_RESETS */], 1ull);
+  return 0;
+}
+
+/* -------------------------------------------------------------------- step */
+/* cog_env::next_agent src/environment.cpp:79-89 */
+__device__ __forceinline__ void env_next_agent(Env &E, u32 &pc, int p, u32 n_players, int lane) {
+  player_end_turn(E, pc, p, lane);
+  if (lane == p) E.pc = pc;
+  E.agent = E.agent + 1;
+  if (E.agent >= n_players) E.agent = 0;
+  E.Splay = bcast(E.Pplay, (int)E.agent); /* load_actionmask */
+  E.Sspec = bcast(E.Pspec, (int)E.agent);
+  E.Srem = bcast(E.Prem, (int)E.agent);
+  E.Sms = bcast(E.Pms, (int)E.agent);
+  res_clear(E);
+  E.turn++;
+}
+
+/* cog_env::step src/environment.cpp:91-224 followed by vec_cog_env::step_single's
+ * auto-reset (include/vec_environment.h:53-61).  `act` = the five ActionData bytes
+ * packed play | special<<8 | remove<<16 | move<<24, shop separately.
+ * Returns: bit0 done, bits 8-11 players whose exported records changed. */
+__device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Params &prm, const Buffers &B,
+                                        u64 i, BoardScratch &sc, int lane) {
+  const u32 a_play = act & 0xffu, a_special = (act >> 8) & 0xffu, a_remove = (act >> 16) & 0xffu,
+            a_move = act >> 24;
+  const int p = (int)E.agent;
+  E.info_steps = addb(E.info_steps, p, 1); /* info.agent_infos[agent].steps_taken++ :97 */
+  if (E.phase == PH_INACTIVE) env_cycle_phase(E);
+  u32 pf = bcast(E.pf, p), pc = bcast(E.pc, p);
+  pf = setb(pf, 3, getb(pf, 3) + 1); /* Player::steps_taken */
+  int special = SP_NONE;
+
+  if (a_play) { /* Player::play_card src/player.cpp:47-69 */
+    const u32 lc = bcast(LANE_CONST[lane], (int)a_play);
+    if (E.phase == PH_MOVEMENT) {
+      E.res[0] = 2 * (int)(lc & 7u);
+      E.res[1] = 2 * (int)((lc >> 3) & 7u);
+      E.res[2] = 2 * (int)((lc >> 6) & 7u);
+    } else if (E.phase == PH_BUYING) {
+      const int coin = (int)((lc >> 6) & 7u);
+      E.res[2] += coin > 0 ? 2 * coin : 1;
+    }
+    deck_activate(E, pc, p, (int)a_play - 1, lane);
+  } else if (a_special) { /* Player::play_special src/player.cpp:71-79 */
+    const u32 lc = bcast(LANE_CONST[lane], (int)a_special);
+    if ((lc >> 9) & 1u) deck_remove_immediate(E, pc, p, (int)a_special - 1, lane);
+    else deck_play_immediate(E, pc, p, (int)a_special - 1, lane);
+    special = (int)((lc >> 10) & 7u);
+  } else if (a_move) { /* Map::move_in_direction src/map.cpp:356-367 */
+    const u32 c = bcast(getb(E.nbr, p), (int)a_move);
+    int dx, dy;
+    dir_delta((int)a_move, dx, dy);
+    const u32 loc = bcast(E.ploc, p);
+    if (lane == p) E.ploc = loc_pack(loc_x(loc) + dx, loc_y(loc) + dy);
+    nbr_refresh(E, B.grid + i * COGL_GRID_BYTES, p, lane);
+    if (!(pf & PFL_MOVE_FREE)) {
+      player_handle_requirement(E, pf, pc, p, hex_req(c), (u32)hex_n(c), lane);
+    } else {
+      pf &= ~(u32)PFL_MOVE_FREE;
+      player_enable_playing(E, p, lane);
+    }
+    if (lane == p) E.pmv++;
+    pf = (pf & ~(u32)PFL_WON) | (u32)hex_end(c);
+  } else {
+    pf &= ~(u32)PFL_MOVE_FREE;
+    if (a_shop) {
+      const int idx = (int)a_shop - 1;
+      int card;
+      if (pf & PFL_CARD_FREE) {
+        card = shop_get(E, idx, lane); /* Shop::transmit */
+      } else {
+        card = shop_buy(E, idx, lane);
+        E.res[2] -= 2 * (int)((bcast(LANE_CONST[lane], card + 1) >> 13) & 7u); /* Player::pay */
+        env_cycle_phase(E);
+      }
+      if (lane == card + 1) E.discard = addb(E.discard, p, 1); /* Deck::add */
+      pf = setb(pf, 2, getb(pf, 2) + 1);
+    } else if (a_remove) {
+      deck_remove_immediate(E, pc, p, (int)a_remove - 1, lane);
+      const u32 nr = (getb(pf, 1) - 1u) & 0xffu;
+      pf = setb(pf, 1, nr);
+      if (!nr) player_enable_playing(E, p, lane);
+      else special = SP_REMOVE_PENDING;
+    } else {
+      env_cycle_phase(E);
+      if (getb(pf, 1) > 0) {
+        pf = setb(pf, 1, 0);
+        player_enable_playing(E, p, lane);
+      }
+    }
+    if (pf & PFL_CARD_FREE) {
+      pf &= ~(u32)PFL_CARD_FREE;
+      player_enable_playing(E, p, lane);
+    }
+  }
+
+  if ((pf & PFL_MIP) && !a_move) {
+    pf &= ~(u32)PFL_MIP;
+    res_clear(E);
+  }
+
+  /* maybe_end_turn :244-250 */
+  if ((pf & PFL_WON) || E.phase == PH_INACTIVE) env_next_agent(E, pc, p, prm.n_players, lane);
+  if (lane == p) { E.pf = pf; E.pc = pc; }
+  const int agent = (int)E.agent;
+  env_update_observation(E, agent, lane);
+  u32 touched = (1u << p) | (1u << agent);
+  u32 done = 0;
+
+  if (special != SP_NONE) { /* :183-186; src/cards.cpp:8-36; remove lambda :156-158 */
+    u32 Pms = bcast(E.Pms, agent);
+    switch (special) {
+    case SP_TRANSMIT: /* transmit_action */
+      Pms = 1u | ((1u | shop_transmit_bits(E, lane)) << 7);
+      player_disable_playing(E);
+      pf |= PFL_CARD_FREE;
+      break;
+    case SP_DRAW2: deck_draw(E, pc, p, 2, lane); break;
+    case SP_DRAW3: deck_draw(E, pc, p, 3, lane); break;
+    case SP_DRAW1_REMOVE1:
+    case SP_DRAW2_REMOVE2: { /* draw_and_remove_action<n, m> */
+      const u32 k = special == SP_DRAW1_REMOVE1 ? 1u : 2u;
+      deck_draw(E, pc, p, k, lane);
+      pf = setb(pf, 1, k);
+      if (lane == agent) E.Prem = E.Pplay; /* P.remove = (stale) P.play */
+      player_disable_playing(E);
+      Pms = (Pms & 0x7fu) | (((Pms >> 7) & 1u) << 7);
+      break;
+    }
+    case SP_NATIVE: { /* native_action: any passable neighbour of the PLAYER who played it */
+      const u32 mv = movement_bits(E, p, 200, 200, 200, 100, lane);
+      Pms = (Pms & 1u) | mv | (((Pms >> 7) & 1u) << 7);
+      pf |= PFL_MOVE_FREE;
+      player_disable_playing(E);
+      break;
+    }
+    default: /* SP_REMOVE_PENDING: shop.set_available_mask(0, mask) */
+      Pms = (Pms & 0x7fu) | (((Pms >> 7) & 1u) << 7);
+      break;
+    }
+    if (lane == agent) E.Pms = Pms;
+    if (lane == p) { E.pf = pf; E.pc = pc; }
+  } else {
+    /* Map::player_done src/map.cpp:407-410 for the NEW current agent, or truncation */
+    const u32 here = bcast(getb(E.nbr, agent), 0);
+    if (hex_end(here) || E.turn >= prm.max_steps) {
+      done = 1;
+      const u32 np = prm.n_players < 4 ? prm.n_players : 4;
+      const bool won = lane < 4 && (E.pf & PFL_WON);
+      const u32 winners = __ballot_sync(COG_FULL, won); /* get_reward :281-288 sums all 4 slots */
+      const int n_winners = __popc(winners);
+      u8 *info = B.infos + i * COGL_INFO_SIZE;
+      if (lane == 0) *reinterpret_cast<u32 *>(info) = E.turn; /* total_length = turn_counter */
+      if (lane < (int)np) {
+        u8 *ai = info + COGL_INFO_AGENT + COGL_INFO_AGENT_STRIDE * lane;
+        const float ret = (float)((int)prm.n_players * (won ? 1 : 0) - n_winners);
+        const u32 added = getb(E.pf, 2);
+        ai[0] = (u8)getb(E.pf, 3);
+        *reinterpret_cast<float *>(ai + 4) = ret;
+        *reinterpret_cast<u32 *>(ai + 8) = E.pmv;
+        ai[12] = (u8)added;
+        ai[13] = (u8)added; /* get_n_removed returns n_added_cards src/player.cpp:224 */
+        *reinterpret_cast<u32 *>(ai + 16) = 0;
+        *reinterpret_cast<u32 *>(ai + 20) = 0;
+        *reinterpret_cast<u32 *>(ai + 24) = 0;
+        *reinterpret_cast<u32 *>(ai + 28) = added; /* get_n_discarded also returns it :223 */
+        B.rewards[i * 4 + lane] = ret;
+      }
+      /* info steps_taken bytes now mirror the players' counters */
+      u32 steps = E.info_steps;
+      for (u32 k = 0; k < np; ++k) steps = setb(steps, (int)k, getb(bcast(E.pf, (int)k), 3));
+      E.info_steps = steps;
+      /* episode aggregates (reduced across GPUs by the host) */
+      const u32 moved = __reduce_add_sync(COG_FULL, lane < (int)np ? E.pmv : 0u);
+      const u32 added = __reduce_add_sync(COG_FULL, lane < (int)np ? getb(E.pf, 2) : 0u);
+      if (lane == 0) {
+        atomicAdd(&B.stats[1], 1ull);
+        if (!n_winners) atomicAdd(&B.stats[2], 1ull);
+        atomicAdd(&B.stats[3], (unsigned long long)E.turn);
+        atomicAdd(&B.stats[8], (unsigned long long)moved);
+        atomicAdd(&B.stats[9], (unsigned long long)added);
+      }
+      if (lane < 4 && won) atomicAdd(&B.stats[4 + lane], 1ull);
+      env_reset(E, prm, B, i, sc, lane); /* auto-reset, the RNG stream continues */
+      touched = 0xfu;
+    }
+  }
+  return done | (touched << 8);
+}
+
+/* ----------------------------------------------------------------- sampler */
+/* action_sampler::sample include/sampler.h:14-79: five heads in the order play,
+ * play_special, remove, move, get_from_shop; each head draws uniformly among its set
+ * bits (one draw even when only index 0 is valid).  `valid` are the head's bit sets. */
+__device__ __forceinline__ u32 sample_head(u32 &rng, u32 valid) {
+  const int k = __popc(valid);
+  if (!k) return 0;
+  const u32 j = uniform_draw(rng, (u32)k);
+  return __fns(valid, 0, (int)j + 1);
+}
+__device__ __forceinline__ void sample_action(u32 &rng, u32 play, u32 spec, u32 rem, u32 ms, u32 &act,
+                                              u32 &a_shop) {
+  const u32 a0 = sample_head(rng, play & 0x3fffffu);
+  const u32 a1 = sample_head(rng, spec & 0x3fffffu);
+  const u32 a2 = sample_head(rng, rem & 0x3fffffu);
+  const u32 a3 = sample_head(rng, ms & 0x7fu);
+  a_shop = sample_head(rng, (ms >> 7) & 0x7ffffu);
+  act = a0 | (a1 << 8) | (a2 << 16) | (a3 << 24);
+}
+
+}  // namespace cog
+#endif /* COG_DEVICE_CUH */

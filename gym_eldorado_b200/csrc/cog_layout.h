@@ -1,0 +1,71 @@
+/* cog_layout.h — byte layouts shared by the kernels and the host C ABI.
+ *
+ * (1) Exported records: the reference's PODs, byte for byte (reference
+ *     include/api.h:67-161, measured offsets in SURVEY App. B).
+ * (2) The private per-env state record in HBM ("hidden" state):
+ *     COG_HID_LINES lines of 32 words.  One warp owns one env and lane l loads
+ *     word l of every line, so each line is ONE fully coalesced 128-byte
+ *     transaction and lands directly in the register that lane keeps it in.
+ */
+#ifndef COG_LAYOUT_H
+#define COG_LAYOUT_H
+#include <stdint.h>
+
+/* ---- exported records ---------------------------------------------------- */
+enum {
+  COGL_OBS_SIZE = 17216,
+  COGL_MAP_BYTES = 48 * 48 * 7, /* 16128 */
+  COGL_OBS_PHASE = 16128,
+  COGL_OBS_RES = 16132,  /* float[3] machete, paddle, coin */
+  COGL_OBS_SHOP = 16144, /* u8[18] */
+  COGL_OBS_PLAYER = 16192,
+  COGL_PLAYER_STRIDE = 256,
+  COGL_DK_DRAW = 0, COGL_DK_HAND = 21, COGL_DK_ACTIVE = 42, COGL_DK_PLAYED = 63, COGL_DK_DISCARD = 84,
+  COGL_PD_MASK = 128,
+  COGL_MASK_SIZE = 128,
+  COGL_AM_PLAY = 0, COGL_AM_SPECIAL = 22, COGL_AM_REMOVE = 44, COGL_AM_MOVE = 66, COGL_AM_SHOP = 73,
+  COGL_AM_PAYLOAD = 92,
+  COGL_ACTION_SIZE = 64,
+  COGL_INFO_SIZE = 192,
+  COGL_INFO_AGENT = 4, COGL_INFO_AGENT_STRIDE = 32,
+  COGL_GRID = 48,
+  COGL_GRID_BYTES = 48 * 48
+};
+
+/* ---- hidden per-env record ------------------------------------------------
+ * line 0..4  card piles draw/hand/active/played/discard: lane l (1..21) holds card
+ *            type l-1, byte p of the word = player p's count
+ * line 5     shop: lane l (1..18) holds slot l-1: bits 0-7 n_available, bit 8 in_market
+ * line 6     neighbour cache: lane d (0..6): byte p = hex code of the hex in direction d
+ *            of player p (d = 0: the hex the player stands on)
+ * line 7     per-player fields, word 4*f + p = field f of player p (COG_PF_*)
+ * line 8     env scalars, word = COG_ES_*
+ */
+enum {
+  COG_HID_LINES = 9,
+  COG_HID_WORDS = COG_HID_LINES * 32,
+  COG_HL_DRAW = 0, COG_HL_HAND = 1, COG_HL_ACTIVE = 2, COG_HL_PLAYED = 3, COG_HL_DISCARD = 4,
+  COG_HL_SHOP = 5, COG_HL_NBR = 6, COG_HL_PLAYER = 7, COG_HL_ENV = 8
+};
+/* per-player fields (line 7) */
+enum {
+  COG_PF_FLAGS = 0, /* bit0 has_won, bit1 movement_in_progress, bit2 next_card_free,
+                       bit3 next_move_free; byte1 n_removes; byte2 n_added_cards; byte3 steps_taken */
+  COG_PF_COUNTS = 1, /* byte0 n_in_hand, byte1 n_active, byte2 n_in_draw, byte3 idx_last_activated */
+  COG_PF_MOVES = 2,  /* n_movements u32 */
+  COG_PF_LOC = 3,    /* int16 x | int16 y << 16, in half-hex units (2x the reference's float) */
+  COG_PF_MPLAY = 4, COG_PF_MSPEC = 5, COG_PF_MREM = 6, /* P[p] mask heads as bit sets */
+  COG_PF_MMS = 7     /* P[p].move (bits 0-6) | P[p].get_from_shop (bits 7-25) */
+};
+/* env scalars (line 8) */
+enum {
+  COG_ES_RNG = 0,        /* minstd_rand0 state of the env */
+  COG_ES_TURN = 1,       /* turn_counter */
+  COG_ES_MISC = 2,       /* byte0 agent_selection, byte1 phase, byte2 n_in_market */
+  COG_ES_RES0 = 3, COG_ES_RES1 = 4, COG_ES_RES2 = 5, /* current_resources * 2 (int32) */
+  COG_ES_MIN = 6,        /* int16 min_x | int16 min_y << 16 (half-hex units) */
+  COG_ES_SPLAY = 7, COG_ES_SSPEC = 8, COG_ES_SREM = 9, COG_ES_SMS = 10, /* S (selected mask) */
+  COG_ES_INFOSTEPS = 11  /* Info.agent_infos[k].steps_taken, byte k */
+};
+
+#endif

@@ -1,0 +1,155 @@
+/* cog_b200.h — C ABI of the B200-native City of Gold vectorised hot path.
+ *
+ * This is the drop-in boundary: every entry point below replaces one member of
+ * the reference's vectorised containers (aapo-kossi/gym-eldorado), which its
+ * pybind module `city_of_gold` binds (reference include/pybind/vectorized.h).
+ * Plain pointers and sizes only; no C++ or torch types cross this line.
+ *
+ * One `cog_vec` handle = one GPU's slice [env_index_offset, +n_envs) of a job.
+ * Seeds derive from the GLOBAL env index, so any sharding of a job over GPUs
+ * gives identical per-env trajectories.  The library owns all device memory;
+ * exported buffers keep the reference's record layouts (include/api.h:67-161)
+ * at device addresses that never change until cog_vec_destroy().
+ *
+ * Calls on one handle must come from one host thread at a time; work is
+ * enqueued on the handle's CUDA stream and is asynchronous unless stated.
+ * Return value: 0 on success, negative cog_status otherwise; the message for
+ * the calling thread's last failure is cog_last_error().
+ */
+#ifndef COG_B200_H
+#define COG_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define COG_API __declspec(dllexport)
+#else
+#define COG_API __attribute__((visibility("default")))
+#endif
+
+/* exported record sizes (reference include/api.h) */
+#define COG_OBS_SIZE 17216
+#define COG_MASK_SIZE 128
+#define COG_MASK_PAYLOAD 92
+#define COG_ACTION_SIZE 64
+#define COG_ACTION_PAYLOAD 5
+#define COG_INFO_SIZE 192
+#define COG_MAX_PLAYERS 4
+
+typedef enum cog_status {
+  COG_OK = 0,
+  COG_ERR_INVALID = -1,      /* bad argument / handle */
+  COG_ERR_MAP_FAILURE = -2,  /* generate_map_failure (reference include/map.h:13-15) */
+  COG_ERR_MAP_BOUNDS = -3,   /* board does not fit the 48x48 observation (UB in the reference) */
+  COG_ERR_CUDA = -4,         /* a CUDA runtime call failed */
+  COG_ERR_NOT_RESET = -5     /* step before the first reset(seed, ...) */
+} cog_status;
+
+/* reference include/constants.h:11 */
+typedef enum cog_difficulty { COG_EASY = 0, COG_MEDIUM = 1, COG_HARD = 2 } cog_difficulty;
+
+/* which exported buffer (reference property in parentheses,
+ * include/pybind/vectorized.h:70-102,200-214) */
+typedef enum cog_buffer {
+  COG_BUF_OBS = 0,             /* observations            ObsData[n]      17216 B */
+  COG_BUF_SELECTED_MASKS = 1,  /* selected_action_masks   ActionMask[n]     128 B */
+  COG_BUF_REWARDS = 2,         /* rewards                 float[n][4]        16 B */
+  COG_BUF_DONES = 3,           /* dones                   bool[n]             1 B */
+  COG_BUF_INFOS = 4,           /* infos                   Info[n]           192 B */
+  COG_BUF_AGENT_SELECTION = 5  /* agent_selection         uint8[n]            1 B */
+} cog_buffer;
+
+/* episode aggregates accumulated on the device since cog_vec_create / the last
+ * cog_vec_stats_reset (the vector ranks all-reduce with NCCL) */
+typedef enum cog_stat {
+  COG_STAT_ENV_STEPS = 0,
+  COG_STAT_EPISODES = 1,       /* finished episodes (= auto-resets) */
+  COG_STAT_TRUNCATIONS = 2,    /* episodes ended by turn_counter >= max_steps without a winner */
+  COG_STAT_TOTAL_LENGTH = 3,   /* sum of Info.total_length (turns) over finished episodes */
+  COG_STAT_WINS_SEAT0 = 4,     /* +seat: episodes that seat won */
+  COG_STAT_TRAVELLED_HEXES = 8,
+  COG_STAT_CARDS_ADDED = 9,
+  COG_STAT_RESETS = 10,        /* boards generated (explicit + auto) */
+  COG_STAT_COUNT = 12
+} cog_stat;
+
+typedef struct cog_vec cog_vec;         /* vec_cog_env<N>        include/vec_environment.h:12-81 */
+typedef struct cog_sampler cog_sampler; /* vec_action_sampler<N> include/vec_sampler.h:7-27 */
+
+COG_API const char *cog_last_error(void);
+COG_API int cog_device_count(int *count);
+
+/* vec_cog_env<N>::vec_cog_env()  (include/vec_environment.h:23-31).
+ * `stream` is a cudaStream_t; NULL = the device's default stream, which also orders the
+ * handle's work against a sampler created with NULL and against torch's default stream. */
+COG_API int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device,
+                           void *stream, cog_vec **out);
+COG_API int cog_vec_destroy(cog_vec *h);
+
+/* vec_cog_env<N>::reset(seed, n_players, n_pieces, difficulty, max_steps, render)
+ * (include/vec_environment.h:38-44 -> src/environment.cpp:42-77).  Env i is seeded
+ * uint32(seed + env_index_offset + i).  Synchronous: returns COG_ERR_MAP_FAILURE
+ * where the reference throws generate_map_failure.  `render` is accepted and
+ * ignored (the reference's rendering is text stubs). */
+COG_API int cog_vec_reset(cog_vec *h, uint32_t seed, uint8_t n_players, uint8_t n_pieces,
+                          int difficulty, uint32_t max_steps, int render);
+/* vec_cog_env<N>::reset()  (include/vec_environment.h:33-37): same parameters,
+ * RNG streams continue. */
+COG_API int cog_vec_reset_default(cog_vec *h);
+
+/* vec_cog_env<N>::step(actions)  (include/vec_environment.h:46-61): one step per
+ * env with auto-reset on done.  `d_actions` is a DEVICE pointer to n_envs
+ * ActionData records (64 B each, 5 payload bytes). */
+COG_API int cog_vec_step(cog_vec *h, const void *d_actions);
+/* same, but `h_actions` is a HOST pointer (what the reference's step(ndarray) gets);
+ * the copy is enqueued on the handle's stream */
+COG_API int cog_vec_step_host(cog_vec *h, const void *h_actions);
+
+/* device address of an exported buffer; stable for the handle's lifetime */
+COG_API int cog_vec_buffer(cog_vec *h, int which, void **d_ptr, size_t *itemsize,
+                           size_t *count);
+/* copy an exported buffer to host memory (synchronises the handle's stream) */
+COG_API int cog_vec_read(cog_vec *h, int which, void *h_dst, size_t nbytes);
+COG_API int cog_vec_num_envs(cog_vec *h, uint64_t *n);
+
+/* vec_action_sampler<N>(seed)  (include/vec_sampler.h:9-13): sampler i is seeded
+ * with the un-truncated 64-bit uint32(seed) + env_index_offset + i. */
+COG_API int cog_sampler_create(uint64_t n_envs, uint64_t env_index_offset, uint32_t seed,
+                               int device, void *stream, cog_sampler **out);
+COG_API int cog_sampler_destroy(cog_sampler *s);
+/* vec_action_sampler<N>::sample(masks)  (include/vec_sampler.h:14-21 ->
+ * include/sampler.h:14-79).  `d_masks`: DEVICE pointer to n_envs ActionMask records. */
+COG_API int cog_sampler_sample(cog_sampler *s, const void *d_masks);
+COG_API int cog_sampler_sample_host(cog_sampler *s, const void *h_masks);
+/* vec_action_sampler<N>::get_actions(): device address of ActionData[n_envs] */
+COG_API int cog_sampler_actions(cog_sampler *s, void **d_ptr);
+COG_API int cog_sampler_read_actions(cog_sampler *s, void *h_dst, size_t nbytes);
+
+/* ThreadedRunner<N> replacement (include/runner.h:21-134): k_steps x
+ * { sample(selected_action_masks); step(actions) } in ONE persistent kernel with
+ * no host round trip; bit-identical to k_steps single sample+step calls.
+ * The sampler's action buffer holds the last sampled actions afterwards. */
+COG_API int cog_vec_run_fused(cog_vec *h, cog_sampler *s, uint64_t k_steps);
+
+/* episode aggregates (COG_STAT_COUNT uint64 values); synchronises the stream */
+COG_API int cog_vec_stats(cog_vec *h, uint64_t *out, size_t n);
+COG_API int cog_vec_stats_reset(cog_vec *h);
+
+/* wait for everything enqueued on the handle; reports deferred device-side
+ * failures (map generation during an auto-reset) */
+COG_API int cog_sync(cog_vec *h);
+/* number of kernels this library has launched on behalf of this process */
+COG_API uint64_t cog_kernel_launches(void);
+/* elapsed device time (ms) of the most recent cog_vec_step / cog_vec_run_fused /
+ * cog_sampler_sample kernel on this handle, measured with CUDA events on the
+ * handle's stream; synchronises */
+COG_API int cog_vec_last_kernel_ms(cog_vec *h, float *ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* COG_B200_H */

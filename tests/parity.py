@@ -1,0 +1,132 @@
+"""Shared parity driver: the C-ABI library (CUDA on a GPU box, or the emulated build
+in tests/emu for CPU-only logic checks) against the oracle, payload bytes only."""
+import os
+import subprocess
+
+import numpy as np
+
+from gym_eldorado_b200 import capi, layout
+from gym_eldorado_b200.layout import payload_bytes as pb
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+EMU_PATH = os.path.join(HERE, "emu", "libcog_emu.so")
+_emu = None
+
+
+def emu_lib():
+    """TEST-ONLY: the kernels compiled for the host under the lock-step warp emulator."""
+    global _emu
+    if _emu is None:
+        subprocess.check_call(["make", "-s", "-C", os.path.join(HERE, "emu")])
+        _emu = capi.load(EMU_PATH)
+    return _emu
+
+
+class Candidate:
+    """vec env + sampler driven through the C ABI, with host snapshots of every buffer."""
+
+    def __init__(self, library, n, sampler_seed, offset=0):
+        self.n = n
+        self.vec = capi.VecHandle(n, offset, 0, None, library)
+        self.smp = capi.SamplerHandle(n, sampler_seed, offset, 0, None, library)
+        self.masks_ptr = self.vec.buffer(layout.BUF_SELECTED_MASKS)[0]
+
+    def reset(self, *a, **k):
+        self.vec.reset(*a, **k)
+
+    def sample(self, masks=None):
+        if masks is None:
+            self.smp.sample_device(self.masks_ptr)
+        else:
+            self.smp.sample_host(np.ascontiguousarray(masks))
+
+    def step(self):
+        self.vec.step_device(self.smp.actions_ptr())
+
+    def snapshot(self):
+        v = self.vec
+        return {
+            "observations": v.read(layout.BUF_OBS),
+            "selected_action_masks": v.read(layout.BUF_SELECTED_MASKS),
+            "rewards": v.read(layout.BUF_REWARDS),
+            "dones": v.read(layout.BUF_DONES),
+            "infos": v.read(layout.BUF_INFOS),
+            "agent_selection": v.read(layout.BUF_AGENT_SELECTION),
+            "actions": self.smp.read_actions(),
+        }
+
+    def close(self):
+        self.vec.close()
+        self.smp.close()
+
+
+def oracle_snapshot(o):
+    return {k: getattr(o, k) for k in ("observations", "selected_action_masks", "rewards", "dones",
+                                       "infos", "agent_selection", "actions")}
+
+
+def merged_masks(snap):
+    """Regime M: S.play/play_special, P[agent].move/get_from_shop,
+    P[agent].remove AND hand > 0 — exercises every branch of step."""
+    n = len(snap["agent_selection"])
+    idx = np.arange(n)
+    pd = snap["observations"]["player_data"][idx, snap["agent_selection"]]
+    m = np.zeros(n, dtype=layout.action_mask_dtype)
+    S = snap["selected_action_masks"]
+    m["play"] = S["play"]
+    m["play_special"] = S["play_special"]
+    m["move"] = pd["action_mask"]["move"]
+    m["get_from_shop"] = pd["action_mask"]["get_from_shop"]
+    rem = pd["action_mask"]["remove"].copy()
+    rem[:, 1:] &= pd["obs"]["hand"] > 0
+    m["remove"] = rem
+    return m
+
+
+def first_mismatch(a, b):
+    for name in ("observations", "selected_action_masks", "infos", "actions"):
+        x, y = pb(a[name]), pb(b[name])
+        if not np.array_equal(x, y):
+            bad = np.argwhere(x != y)
+            return "%s: env %d payload byte %d: %d != %d (%d bytes differ)" % (
+                name, bad[0][0], bad[0][1], x[tuple(bad[0])], y[tuple(bad[0])], len(bad))
+    for name in ("rewards", "dones", "agent_selection"):
+        if not np.array_equal(np.asarray(a[name]), np.asarray(b[name])):
+            return name
+    return None
+
+
+def run_parity(library, oracle_cls, n, seed, difficulty, max_steps, steps, regime, n_players=4,
+               n_pieces=3, check_every=1, offset=0):
+    """Drive candidate and oracle side by side; returns the number of dones seen."""
+    o = oracle_cls(n, seed) if offset == 0 else oracle_cls(n, seed, offset)
+    c = Candidate(library, n, seed, offset)
+    try:
+        o.reset(seed, n_players, n_pieces, difficulty, max_steps)
+        c.reset(seed, n_players, n_pieces, difficulty, max_steps)
+        snap = c.snapshot()
+        bad = first_mismatch(snap, oracle_snapshot(o))
+        assert bad is None, "after reset: " + bad
+        dones = 0
+        for s in range(steps):
+            if regime == "A":
+                o.sample()
+                c.sample()
+            else:
+                if check_every != 1:
+                    snap = c.snapshot()
+                m = merged_masks(snap)
+                o.sample(m)
+                c.sample(m)
+            o.step()
+            c.step()
+            dones += int(o.dones.sum())
+            if regime != "A" or (s + 1) % check_every == 0 or s == steps - 1:
+                snap = c.snapshot()
+            if (s + 1) % check_every == 0 or s == steps - 1:
+                bad = first_mismatch(snap, oracle_snapshot(o))
+                assert bad is None, "step %d: %s" % (s, bad)
+        return dones
+    finally:
+        c.close()
+        o.close()
