@@ -1,0 +1,48 @@
+"""CPU: the kernels' game logic, compiled for the host under the lock-step warp
+emulator (tests/emu — test infrastructure, never loaded by the package), against the
+oracle.  Same driver as the GPU parity tests, smaller sizes."""
+import pytest
+
+import parity
+from gym_eldorado_b200 import capi, layout
+
+
+@pytest.mark.parametrize("n,seed,difficulty,max_steps,steps,regime,n_players", [
+    (16, 0, layout.EASY, 100000, 300, "A", 4),
+    (16, 777, layout.EASY, 100000, 700, "M", 4),
+    (16, 777, layout.HARD, 60, 700, "M", 4),
+    (16, 12345, layout.MEDIUM, 30, 700, "M", 4),
+    (8, 99, layout.HARD, 8, 300, "M", 2),
+    (8, 99, layout.HARD, 8, 300, "A", 3),
+])
+def test_emulated_trajectory_parity(emu, oracle_cls, n, seed, difficulty, max_steps, steps, regime, n_players):
+    parity.run_parity(emu, oracle_cls, n, seed, difficulty, max_steps, steps, regime, n_players=n_players)
+
+
+def test_emulated_fused_equals_single(emu, oracle_cls):
+    n, seed, k = 12, 2024, 120
+    o = oracle_cls(n, seed)
+    o.reset(seed, 4, 3, layout.HARD, 8)
+    for _ in range(k):
+        o.sample()
+        o.step()
+    a = parity.Candidate(emu, n, seed)
+    a.reset(seed, 4, 3, layout.HARD, 8)
+    for chunk in (1, 0, 19, k - 20):
+        a.vec.run_fused(a.smp, chunk)
+    assert parity.first_mismatch(a.snapshot(), parity.oracle_snapshot(o)) is None
+    st = a.vec.stats()
+    assert st["env_steps"] == n * k and st["resets"] == n + st["episodes"] and st["episodes"] > 0
+    a.close(); o.close()
+
+
+def test_emulated_map_failure(emu):
+    c = parity.Candidate(emu, 4, 0)
+    with pytest.raises(capi.MapGenerationError):
+        c.reset(123, 3, 4, layout.EASY, 100)
+    c.reset(124, 3, 3, layout.EASY, 100)
+    c.close()
+
+
+def test_emulated_offset_shard(emu, oracle_cls):
+    parity.run_parity(emu, oracle_cls, 8, 31337, layout.MEDIUM, 50, 150, "M", offset=1000)

@@ -1,0 +1,119 @@
+"""GPU parity tests: the CUDA kernels, called through the C ABI, against the oracle.
+Bit-exact on every payload byte of every exported buffer (integer/byte work; the only
+floats are small multiples of 0.5 and integers, compared exactly)."""
+import numpy as np
+import pytest
+
+import parity
+from gym_eldorado_b200 import layout
+from gym_eldorado_b200.layout import payload_bytes as pb
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("n,seed,difficulty,max_steps,steps,regime,n_players", [
+    (16, 0, layout.EASY, 100000, 1000, "A", 4),        # BASELINE config 1 (README example)
+    (256, 12345, layout.EASY, 100000, 2000, "A", 4),   # BASELINE config 2 (asv loop), every step
+    (256, 777, layout.EASY, 100000, 1500, "M", 4),     # every branch of step, wins, auto-resets
+    (256, 777, layout.HARD, 60, 1500, "M", 4),
+    (256, 12345, layout.MEDIUM, 30, 1500, "M", 4),
+    (128, 99, layout.HARD, 8, 600, "M", 2),            # BASELINE config 4 shape (2 players)
+    (128, 99, layout.HARD, 8, 600, "A", 3),
+    (64, 4242, layout.HARD, 8, 400, "M", 1),
+])
+def test_trajectory_parity(cuda_lib, oracle_cls, n, seed, difficulty, max_steps, steps, regime, n_players):
+    parity.run_parity(cuda_lib, oracle_cls, n, seed, difficulty, max_steps, steps, regime,
+                      n_players=n_players)
+
+
+def test_seed_wraps_and_offsets(cuda_lib, oracle_cls):
+    # env seed is uint32(seed + i); a shard with an index offset replays its slice of the job
+    parity.run_parity(cuda_lib, oracle_cls, 64, 0xFFFFFFF0, layout.MEDIUM, 50, 300, "M")
+    parity.run_parity(cuda_lib, oracle_cls, 64, 31337, layout.MEDIUM, 50, 300, "M", offset=1000)
+
+
+@pytest.mark.parametrize("difficulty", [layout.EASY, layout.MEDIUM, layout.HARD])
+def test_boards_on_reset(cuda_lib, oracle_cls, difficulty):
+    """Procedural board generation + 48x48x7 encode: 2048 boards per difficulty."""
+    n = 2048
+    for seed, n_pieces in ((1, 3), (500000, 2), (77, 1)):
+        o = oracle_cls(n, 0)
+        c = parity.Candidate(cuda_lib, n, 0)
+        o.reset(seed, 4, n_pieces, difficulty, 100)
+        c.reset(seed, 4, n_pieces, difficulty, 100)
+        snap = c.snapshot()
+        assert parity.first_mismatch(snap, parity.oracle_snapshot(o)) is None
+        # reset() without arguments: RNG streams continue (include/vec_environment.h:33-37)
+        o.reset()
+        c.reset()
+        assert parity.first_mismatch(c.snapshot(), parity.oracle_snapshot(o)) is None
+        c.close()
+        o.close()
+
+
+def test_map_failure_is_reported(cuda_lib):
+    """EASY has only 3 travel pieces: n_pieces=4 throws generate_map_failure in the
+    reference (src/tests/test_environment.cpp:68-80) -> MapGenerationError here."""
+    from gym_eldorado_b200 import capi
+    c = parity.Candidate(cuda_lib, 32, 0)
+    with pytest.raises(capi.MapGenerationError):
+        c.reset(123, 3, 4, layout.EASY, 100)
+    c.reset(124, 3, 3, layout.EASY, 100)  # and the handle stays usable
+    c.close()
+
+
+@pytest.mark.parametrize("n,difficulty,max_steps,k", [(512, layout.MEDIUM, 100000, 300), (512, layout.HARD, 8, 300)])
+def test_fused_equals_single_steps(cuda_lib, oracle_cls, n, difficulty, max_steps, k):
+    """The persistent fused kernel == k x (sample(selected masks); step), bit for bit,
+    and both == the oracle."""
+    seed = 2024
+    o = oracle_cls(n, seed)
+    o.reset(seed, 4, 3, difficulty, max_steps)
+    for _ in range(k):
+        o.sample()
+        o.step()
+    a = parity.Candidate(cuda_lib, n, seed)
+    a.reset(seed, 4, 3, difficulty, max_steps)
+    for chunk in (1, 7, k - 8):
+        a.vec.run_fused(a.smp, chunk)
+    b = parity.Candidate(cuda_lib, n, seed)
+    b.reset(seed, 4, 3, difficulty, max_steps)
+    for _ in range(k):
+        b.sample()
+        b.step()
+    sa, sb = a.snapshot(), b.snapshot()
+    assert parity.first_mismatch(sa, sb) is None
+    assert parity.first_mismatch(sa, parity.oracle_snapshot(o)) is None
+    st = a.vec.stats()
+    assert st["env_steps"] == n * k
+    assert st["resets"] == n + st["episodes"]
+    a.close(); b.close(); o.close()
+
+
+def test_full_size_properties(cuda_lib):
+    """BASELINE config 3 size (65 536 envs, MEDIUM): properties that need no oracle run.
+    Shards replay the same envs; masks stay self-consistent; stats add up."""
+    n, seed, k = 65536, 12345, 200
+    whole = parity.Candidate(cuda_lib, n, seed)
+    whole.reset(seed, 4, 3, layout.MEDIUM, 100000)
+    whole.vec.run_fused(whole.smp, k)
+    w = whole.snapshot()
+    # a shard [40000, 40000+4096) of the same job reproduces its slice exactly
+    off, m = 40000, 4096
+    part = parity.Candidate(cuda_lib, m, seed, offset=off)
+    part.reset(seed, 4, 3, layout.MEDIUM, 100000)
+    part.vec.run_fused(part.smp, k)
+    p = part.snapshot()
+    for name in ("observations", "selected_action_masks", "infos", "actions"):
+        assert np.array_equal(pb(w[name][off:off + m]), pb(p[name]))
+    for name in ("rewards", "dones", "agent_selection"):
+        assert np.array_equal(w[name][off:off + m], p[name])
+    obs = w["observations"]
+    # card conservation: regime A never buys or removes, so every deck still has 8 cards
+    decks = obs["player_data"]["obs"]
+    total = sum(decks[f].astype(np.int64).sum(axis=2) for f in ("draw", "hand", "active", "played", "discard"))
+    assert (total == 8).all()
+    assert (obs["shared"]["map"][..., 0] == 0).all()          # feature 0 is never written
+    assert (w["selected_action_masks"]["play"][:, 0]).all()    # index 0 always valid
+    assert whole.vec.stats()["env_steps"] == n * k
+    whole.close(); part.close()
