@@ -130,3 +130,22 @@ def run_parity(library, oracle_cls, n, seed, difficulty, max_steps, steps, regim
     finally:
         c.close()
         o.close()
+
+
+def emu_module():
+    """TEST-ONLY: the pybind host module (csrc/pybind_module.cpp) linked against the
+    emulated library, so the reference-style Python loop can be exercised without a GPU."""
+    import importlib.util
+    import sysconfig
+    from gym_eldorado_b200 import pybind_build
+    emu_lib()
+    emu_dir = os.path.join(HERE, "emu")
+    target = os.path.join(emu_dir, "city_of_gold_emu" + sysconfig.get_config_var("EXT_SUFFIX"))
+    deps = [pybind_build.SRC, EMU_PATH]
+    if not os.path.exists(target) or any(os.path.getmtime(d) > os.path.getmtime(target) for d in deps):
+        pybind_build.compile_module(target, emu_dir, "libcog_emu.so", "city_of_gold_emu",
+                                    extra=("-DCOG_HOST_POINTERS",))
+    spec = importlib.util.spec_from_file_location("city_of_gold_emu", target)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
