@@ -134,9 +134,44 @@ __device__ __forceinline__ u32 minstd_next(u32 &s) {
 }
 /* std::uniform_int_distribution<size_t>(0, n-1)(minstd_rand0): the "two divisions"
  * downscaling branch of libstdc++ bits/uniform_int_dist.h:332-340 (the engine's
- * range 2^31-3 is not 2^k-1, so Lemire's path is not taken).  A draw is consumed
- * even for n == 1; rejection makes the count data dependent. */
+ * range 2^31-3 is not 2^k-1, so Lemire's path is not taken):
+ *     scaling = 2147483645 / n;  past = n * scaling;
+ *     do r = g() - 1; while (r >= past);  return r / scaling;
+ * A draw is consumed even for n == 1; rejection makes the count data dependent.
+ * Both divisions are avoided for n <= 32 (every draw of the step/sample path): scaling
+ * and past come from a constant table indexed by the warp-uniform n, and r / scaling is
+ * a multiply-high by magic = floor(2^36 / scaling) + 1 — an over-estimate by less than
+ * r / 2^36 < 1/32, so at most one too large — followed by one exact correction. */
+struct ud_entry { u32 scaling, past, magic, pad; };
+namespace tab {
+constexpr ud_entry ud_make(u32 n) {
+  if (n == 0) return ud_entry{0, 0, 0, 0};
+  const u32 s = 2147483645u / n;
+  return ud_entry{s, n * s, (u32)((1ull << 36) / s) + 1u, 0};
+}
+}  // namespace tab
+#define COG_UD(n) tab::ud_make(n)
+__constant__ const ud_entry UD_TAB[33] = {
+    COG_UD(0),  COG_UD(1),  COG_UD(2),  COG_UD(3),  COG_UD(4),  COG_UD(5),  COG_UD(6),  COG_UD(7),  COG_UD(8),
+    COG_UD(9),  COG_UD(10), COG_UD(11), COG_UD(12), COG_UD(13), COG_UD(14), COG_UD(15), COG_UD(16), COG_UD(17),
+    COG_UD(18), COG_UD(19), COG_UD(20), COG_UD(21), COG_UD(22), COG_UD(23), COG_UD(24), COG_UD(25), COG_UD(26),
+    COG_UD(27), COG_UD(28), COG_UD(29), COG_UD(30), COG_UD(31), COG_UD(32)};
+
 __device__ __forceinline__ u32 uniform_draw(u32 &s, u32 n) {
+  if (n == 1) { /* scaling = past = 2147483645: only g() == 2147483646 is rejected; result 0 */
+    while (minstd_next(s) == 2147483646u) {}
+    return 0;
+  }
+  if (n <= 32) {
+    const ud_entry e = UD_TAB[n];
+    u32 r;
+    do {
+      r = minstd_next(s) - 1u;
+    } while (r >= e.past);
+    u32 q = __umulhi(r, e.magic) >> 4;
+    if (q * e.scaling > r) --q;
+    return q;
+  }
   const u32 scaling = 2147483645u / n;
   const u32 past = n * scaling;
   u32 r;
@@ -144,6 +179,12 @@ __device__ __forceinline__ u32 uniform_draw(u32 &s, u32 n) {
     r = minstd_next(s) - 1u;
   } while (r >= past);
   return r / scaling;
+}
+
+/* position of the (j+1)-th set bit of v (j < popc(v)): clear the j lowest set bits */
+__device__ __forceinline__ u32 nth_set_bit(u32 v, u32 j) {
+  for (u32 t = 0; t < j; ++t) v &= v - 1u;
+  return (u32)__ffs((int)v) - 1u;
 }
 
 /* one +60 degree step in half-hex axial coordinates: (x, y) -> (-y, x + y)
@@ -717,7 +758,7 @@ __device__ __forceinline__ int bg_add_random_piece(BoardScratch &sc, BoardState 
   const int k = __ffs((int)hit) - 1;
   const u32 vm = bcast(my_valid, k);
   const u32 within = idx - (bcast(incl, k) - bcast(cnt, k));
-  const int e = (int)__fns(vm, 0, (int)within + 1);
+  const int e = (int)nth_set_bit(vm, within);
   const int host = sc.placed[k].piece;
   int kind, n_alt = 1, first_opt = 0, n_opts = 1;
   bg_conn_kind(host, piece, kind, n_alt, first_opt, n_opts);
@@ -1108,7 +1149,7 @@ __device__ __forceinline__ u32 sample_head(u32 &rng, u32 valid) {
   const int k = __popc(valid);
   if (!k) return 0;
   const u32 j = uniform_draw(rng, (u32)k);
-  return __fns(valid, 0, (int)j + 1);
+  return nth_set_bit(valid, j);
 }
 __device__ __forceinline__ void sample_action(u32 &rng, u32 play, u32 spec, u32 rem, u32 ms, u32 &act,
                                               u32 &a_shop) {

@@ -28,6 +28,7 @@
 #define __host__
 #define __forceinline__ inline __attribute__((always_inline))
 #define __shared__
+#define __constant__
 #define __launch_bounds__(...)
 
 using std::max;
