@@ -97,12 +97,13 @@ public:
     return d;
   }
 
-  py::capsule dlpack(py::object /*stream*/) const {
+  /* legacy (unversioned) capsule; extra protocol keywords (max_version, copy, dl_device) are accepted */
+  py::capsule dlpack(py::object /*stream*/, py::kwargs /*unused*/) const {
     struct Ctx { std::vector<int64_t> shape; std::shared_ptr<VecOwner> v; std::shared_ptr<SamplerOwner> s; };
     auto *ctx = new Ctx{shape, vec, sampler};
     auto *mt = new DLManagedTensor{};
     mt->dl_tensor.data = ptr;
-    mt->dl_tensor.device = DLDevice{device < 0 ? kDLCPU : kDLCUDA, device < 0 ? 0 : device};
+    mt->dl_tensor.device = DLDevice{(int32_t)(device < 0 ? kDLCPU : kDLCUDA), device < 0 ? 0 : device};
     mt->dl_tensor.ndim = (int32_t)ctx->shape.size();
     mt->dl_tensor.dtype = dl;
     mt->dl_tensor.shape = ctx->shape.data();
@@ -121,7 +122,7 @@ public:
     });
   }
 
-  py::tuple dlpack_device() const { return py::make_tuple(device < 0 ? kDLCPU : kDLCUDA, device < 0 ? 0 : device); }
+  py::tuple dlpack_device() const { return py::make_tuple((int)(device < 0 ? kDLCPU : kDLCUDA), device < 0 ? 0 : device); }
 
   py::array numpy(py::object out) const {
     py::array arr;
@@ -289,7 +290,9 @@ public:
 /* get_vec_env(N) & co. return CLASS objects named like the reference's
  * (vec_cog_env_N, vec_sampler_N, vec_runner_N; src/pybind/vectorized.cpp:8-21) */
 py::object sized_class(const py::object &base, const std::string &name, uint64_t n, bool is_runner) {
-  static py::dict cache;
+  /* the cache lives on the base class object, so it dies with the interpreter, not after it */
+  if (!py::hasattr(base, "_sized")) py::setattr(base, "_sized", py::dict());
+  py::dict cache = base.attr("_sized");
   py::str key(name);
   if (cache.contains(key)) return cache[key];
   py::dict ns;

@@ -96,6 +96,11 @@ def test_python_api_emulated(oracle_cls):
     assert v.shape == (4, layout.obs_dtype.itemsize) and v.dtype == np.uint8
     assert np.array_equal(v.view(layout.obs_dtype).reshape(4)["shared"]["shop"], envs.observations.numpy()["shared"]["shop"])
     assert np.from_dlpack(envs.rewards).shape == (4, 4)
+    import torch  # the consumer the GPU path is meant for; here it sees a CPU capsule
+    t = torch.from_dlpack(envs.observations)
+    assert t.shape == (4, layout.obs_dtype.itemsize) and t.dtype == torch.uint8
+    assert t.data_ptr() == envs.observations.device_pointer
+    assert torch.from_dlpack(envs.dones).dtype == torch.bool
 
 
 @pytest.mark.gpu
