@@ -348,6 +348,7 @@ int cog_vec_run_fused(cog_vec *h, cog_sampler *s, uint64_t k_steps) {
   if (!h || !s) return fail(COG_ERR_INVALID, "NULL argument");
   if (s->n != h->n || s->device != h->device) return fail(COG_ERR_INVALID, "sampler and envs differ in size or device");
   if (!h->seeded) return fail(COG_ERR_NOT_RESET, "run() before reset()");
+  if (k_steps > 0xffffffffull) return fail(COG_ERR_INVALID, "k_steps must fit 32 bits");
   CK(cudaSetDevice(h->device));
   if (s->stream != h->stream) CK(cudaStreamSynchronize(s->stream));
   /* persistent grid: every SM filled once, warps walk the envs with a grid stride */

@@ -108,9 +108,11 @@ __device__ __forceinline__ u32 warp_incl_scan(u32 v, int lane) {
   }
   return v;
 }
-__device__ __forceinline__ u32 getb(u32 w, int p) { return (w >> (8 * p)) & 0xffu; }
+/* byte p of a word, as one PRMT each: the selector is a constant when p is, and is
+ * computed once per step (common subexpression) when p is the current player */
+__device__ __forceinline__ u32 getb(u32 w, int p) { return __byte_perm(w, 0u, 0x4440u | (u32)p); }
 __device__ __forceinline__ u32 setb(u32 w, int p, u32 v) {
-  return (w & ~(0xffu << (8 * p))) | ((v & 0xffu) << (8 * p));
+  return __byte_perm(w, v, 0x3210u + ((4u - (u32)p) << (4 * p)));
 }
 /* u8 arithmetic inside byte p (wraps like the reference's u_char counters) */
 __device__ __forceinline__ u32 addb(u32 w, int p, int d) { return setb(w, p, getb(w, p) + (u32)d); }
@@ -1146,18 +1148,44 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
  * play_special, remove, move, get_from_shop; each head draws uniformly among its set
  * bits (one draw even when only index 0 is valid).  `valid` are the head's bit sets. */
 __device__ __forceinline__ u32 sample_head(u32 &rng, u32 valid) {
-  const int k = __popc(valid);
-  if (!k) return 0;
-  const u32 j = uniform_draw(rng, (u32)k);
+  if (valid == 1u) { /* only "none" is legal: the draw over [0, 0] is still consumed */
+    while (minstd_next(rng) == 2147483646u) {}
+    return 0;
+  }
+  if (!valid) return 0;
+  const u32 j = uniform_draw(rng, (u32)__popc(valid));
   return nth_set_bit(valid, j);
 }
+/* Four consecutive draws over [0, 0] (heads whose only legal index is "none") advance
+ * the engine four times and reject only an output of 2147483646 = -1 (mod m).  Output i
+ * equals x a^i, so no rejection happens unless x = -a^-i for some i in 1..4; otherwise
+ * the four steps collapse into ONE modular multiply by a^4 mod m.  Returns false (state
+ * untouched) in the 4-in-2^31 case that needs the step-by-step path. */
+__device__ __forceinline__ bool minstd_skip4_unit_draws(u32 &s) {
+  if (s == 739806647u || s == 671875339u || s == 939811632u || s == 1785685951u) return false;
+  const u64 t = (u64)s * 984943658ull;                 /* 16807^4 mod (2^31 - 1) */
+  const u64 f = (t & 0x7fffffffull) + (t >> 31);       /* < 2^32 */
+  u32 r = (u32)(f & 0x7fffffffull) + (u32)(f >> 31);
+  if (r >= 0x7fffffffu) r -= 0x7fffffffu;
+  s = r;
+  return true;
+}
+
 __device__ __forceinline__ void sample_action(u32 &rng, u32 play, u32 spec, u32 rem, u32 ms, u32 &act,
                                               u32 &a_shop) {
   const u32 a0 = sample_head(rng, play & 0x3fffffu);
-  const u32 a1 = sample_head(rng, spec & 0x3fffffu);
-  const u32 a2 = sample_head(rng, rem & 0x3fffffu);
-  const u32 a3 = sample_head(rng, ms & 0x7fu);
-  a_shop = sample_head(rng, (ms >> 7) & 0x7ffffu);
+  spec &= 0x3fffffu;
+  rem &= 0x3fffffu;
+  const u32 mv = ms & 0x7fu, shop = (ms >> 7) & 0x7ffffu;
+  if ((spec | rem | mv | shop) == 1u && (spec & rem & mv & shop) == 1u && minstd_skip4_unit_draws(rng)) {
+    a_shop = 0; /* the reference's own flow: only `play` ever has a choice (SURVEY A#2) */
+    act = a0;
+    return;
+  }
+  const u32 a1 = sample_head(rng, spec);
+  const u32 a2 = sample_head(rng, rem);
+  const u32 a3 = sample_head(rng, mv);
+  a_shop = sample_head(rng, shop);
   act = a0 | (a1 << 8) | (a2 << 16) | (a3 << 24);
 }
 

@@ -62,8 +62,11 @@ __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed)
  * FUSED = true : persistent; each warp walks envs with a grid stride, keeps the env in
  *                registers for k_steps x {sample; step}, then writes it back once.
  *                `srng` is the sampler's RNG array, `actions` receives the last action. */
+#ifndef COG_MIN_BLOCKS
+#define COG_MIN_BLOCKS 1
+#endif
 template <bool FUSED>
-__global__ void k_step(Buffers B, Params prm, u64 n, const u8 *__restrict__ actions_in, u32 *srng,
+__global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step(Buffers B, Params prm, u64 n, const u8 *__restrict__ actions_in, u32 *srng,
                        u8 *actions_out, u64 k_steps) {
   const int lane = threadIdx.x & 31;
   const u64 warp0 = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
@@ -77,7 +80,7 @@ __global__ void k_step(Buffers B, Params prm, u64 n, const u8 *__restrict__ acti
     if (FUSED) {
       u32 sr = srng[i];
       u32 act = 0, a_shop = 0, touched = 0;
-      for (u64 k = 0; k < k_steps; ++k) {
+      for (u32 k = 0; k < (u32)k_steps; ++k) {
         sample_action(sr, E.Splay, E.Sspec, E.Srem, E.Sms, act, a_shop);
         status = env_step(E, act, a_shop, prm, B, i, sc, lane);
         touched |= status >> 8;

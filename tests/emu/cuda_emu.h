@@ -205,6 +205,17 @@ static inline unsigned __fns(unsigned mask, unsigned base, int offset) {
       if (--offset == 0) return b;
   return 0xffffffffu;
 }
+static inline unsigned __byte_perm(unsigned a, unsigned b, unsigned sel) {
+  const uint64_t both = ((uint64_t)b << 32) | a;
+  unsigned r = 0;
+  for (int i = 0; i < 4; ++i) {
+    const unsigned n = (sel >> (4 * i)) & 0xf;
+    unsigned byte = (unsigned)(both >> (8 * (n & 7))) & 0xffu;
+    if (n & 8) byte = (byte & 0x80u) ? 0xffu : 0u; /* sign-replicate mode */
+    r |= byte << (8 * i);
+  }
+  return r;
+}
 static inline unsigned __umulhi(unsigned a, unsigned b) { return (unsigned)(((uint64_t)a * b) >> 32); }
 
 /* lanes run one at a time, so plain read-modify-write is atomic */
