@@ -27,6 +27,10 @@ typedef uint8_t u8;
 typedef uint32_t u32;
 typedef uint64_t u64;
 #define COG_FULL 0xffffffffu
+/* branch-layout hints: keep rarely taken paths (episode end + board generation, PRNG
+ * rejections) out of the hot instruction stream */
+#define COG_UNLIKELY(x) __builtin_expect(!!(x), 0)
+#define COG_LIKELY(x) __builtin_expect(!!(x), 1)
 
 /* ------------------------------------------------------------------ tables */
 struct card_def { u8 cost, market, single, res0, res1, res2, special; };
@@ -161,7 +165,7 @@ __constant__ const ud_entry UD_TAB[33] = {
 
 __device__ __forceinline__ u32 uniform_draw(u32 &s, u32 n) {
   if (n == 1) { /* scaling = past = 2147483645: only g() == 2147483646 is rejected; result 0 */
-    while (minstd_next(s) == 2147483646u) {}
+    while (COG_UNLIKELY(minstd_next(s) == 2147483646u)) {}
     return 0;
   }
   if (n <= 32) {
@@ -169,7 +173,7 @@ __device__ __forceinline__ u32 uniform_draw(u32 &s, u32 n) {
     u32 r;
     do {
       r = minstd_next(s) - 1u;
-    } while (r >= e.past);
+    } while (COG_UNLIKELY(r >= e.past));
     u32 q = __umulhi(r, e.magic) >> 4;
     if (q * e.scaling > r) --q;
     return q;
@@ -1062,7 +1066,7 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
   u32 touched = (1u << p) | (1u << agent);
   u32 done = 0;
 
-  if (special != SP_NONE) { /* :183-186; src/cards.cpp:8-36; remove lambda :156-158 */
+  if (COG_UNLIKELY(special != SP_NONE)) { /* :183-186; src/cards.cpp:8-36; remove lambda :156-158 */
     u32 Pms = bcast(E.Pms, agent);
     switch (special) {
     case SP_TRANSMIT: /* transmit_action */
@@ -1098,7 +1102,7 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
   } else {
     /* Map::player_done src/map.cpp:407-410 for the NEW current agent, or truncation */
     const u32 here = bcast(getb(E.nbr, agent), 0);
-    if (hex_end(here) || E.turn >= prm.max_steps) {
+    if (COG_UNLIKELY(hex_end(here) || E.turn >= prm.max_steps)) {
       done = 1;
       const u32 np = prm.n_players < 4 ? prm.n_players : 4;
       const bool won = lane < 4 && (E.pf & PFL_WON);
@@ -1149,7 +1153,7 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
  * bits (one draw even when only index 0 is valid).  `valid` are the head's bit sets. */
 __device__ __forceinline__ u32 sample_head(u32 &rng, u32 valid) {
   if (valid == 1u) { /* only "none" is legal: the draw over [0, 0] is still consumed */
-    while (minstd_next(rng) == 2147483646u) {}
+    while (COG_UNLIKELY(minstd_next(rng) == 2147483646u)) {}
     return 0;
   }
   if (!valid) return 0;
@@ -1162,7 +1166,7 @@ __device__ __forceinline__ u32 sample_head(u32 &rng, u32 valid) {
  * the four steps collapse into ONE modular multiply by a^4 mod m.  Returns false (state
  * untouched) in the 4-in-2^31 case that needs the step-by-step path. */
 __device__ __forceinline__ bool minstd_skip4_unit_draws(u32 &s) {
-  if (s == 739806647u || s == 671875339u || s == 939811632u || s == 1785685951u) return false;
+  if (COG_UNLIKELY(s == 739806647u || s == 671875339u || s == 939811632u || s == 1785685951u)) return false;
   const u64 t = (u64)s * 984943658ull;                 /* 16807^4 mod (2^31 - 1) */
   const u64 f = (t & 0x7fffffffull) + (t >> 31);       /* < 2^32 */
   u32 r = (u32)(f & 0x7fffffffull) + (u32)(f >> 31);

@@ -63,7 +63,7 @@ __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed)
  *                registers for k_steps x {sample; step}, then writes it back once.
  *                `srng` is the sampler's RNG array, `actions` receives the last action. */
 #ifndef COG_MIN_BLOCKS
-#define COG_MIN_BLOCKS 1
+#define COG_MIN_BLOCKS 8
 #endif
 template <bool FUSED>
 __global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step(Buffers B, Params prm, u64 n, const u8 *__restrict__ actions_in, u32 *srng,
