@@ -232,6 +232,7 @@ struct Env {
   u32 draw, hand, active, played, discard;
   u32 shop; /* lane l <-> slot l-1: bits 0-7 stock, bit 8 in_market */
   u32 nbr;  /* lane d <-> direction d: byte p = hex code next to player p */
+  u32 lc;   /* LANE_CONST[lane]: card / shop-slot constants of this lane (not stored) */
   /* lane p <-> player p */
   u32 pf, pc, pmv, ploc, Pplay, Pspec, Prem, Pms;
   /* warp-uniform */
@@ -248,6 +249,7 @@ __device__ __forceinline__ u32 loc_pack(int x, int y) {
 }
 
 __device__ __forceinline__ void env_load(Env &E, const u32 *__restrict__ rec, int lane) {
+  E.lc = LANE_CONST[lane];
   E.draw = rec[COG_HL_DRAW * 32 + lane];
   E.hand = rec[COG_HL_HAND * 32 + lane];
   E.active = rec[COG_HL_ACTIVE * 32 + lane];
@@ -433,7 +435,7 @@ __device__ __forceinline__ void deck_play_last_activated(Env &E, u32 &pc, int p,
   pc = setb(pc, 1, getb(pc, 1) - 1);
   if (lane == cl) {
     E.active = addb(E.active, p, -1);
-    if (!((LANE_CONST[lane] >> 9) & 1u)) E.played = addb(E.played, p, 1);
+    if (!((E.lc >> 9) & 1u)) E.played = addb(E.played, p, 1);
   }
 }
 /* Deck::play_immediate src/cards.cpp:263-273 */
@@ -554,7 +556,7 @@ __device__ __forceinline__ int shop_buy(Env &E, int idx, int lane) {
 /* Shop::set_available_mask src/cards.cpp:109-121: bits 1..18 of get_from_shop.
  * coin2 = coins * 2; the comparison is strict (coins > cost). */
 __device__ __forceinline__ u32 shop_available_bits(const Env &E, int coin2, int lane) {
-  const int cost = (int)((LANE_CONST[lane] >> 16) & 7u);
+  const int cost = (int)((E.lc >> 16) & 7u);
   const bool open = E.n_in_market < 6 ? (E.shop & 0xffu) > 0 : ((E.shop >> 8) & 1u) != 0;
   return __ballot_sync(COG_FULL, lane >= 1 && lane <= 18 && open && coin2 > 2 * cost);
 }
@@ -948,7 +950,7 @@ __device__ __forceinline__ int env_reset(Env &E, const Params &prm, const Buffer
   if (lane < np) E.ploc = loc_pack(COORDS_LARGE[lane].x, COORDS_LARGE[lane].y);
   for (int p = 0; p < np; ++p) nbr_refresh(E, grid, p, lane);
   /* Shop::reset src/cards.cpp:94-100 (n_in_market is NOT reset) */
-  E.shop = (lane >= 1 && lane <= 18) ? (3u | (((LANE_CONST[lane] >> 19) & 1u) << 8)) : 0u;
+  E.shop = (lane >= 1 && lane <= 18) ? (3u | (((E.lc >> 19) & 1u) << 8)) : 0u;
   E.turn = 0;
   for (int p = 0; p < np; ++p) env_update_observation(E, p, lane);
   E.Splay = bcast(E.Pplay, 0); /* load_actionmask of agent 0 :62-63 */
@@ -990,7 +992,7 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
   int special = SP_NONE;
 
   if (a_play) { /* Player::play_card src/player.cpp:47-69 */
-    const u32 lc = bcast(LANE_CONST[lane], (int)a_play);
+    const u32 lc = bcast(E.lc, (int)a_play);
     if (E.phase == PH_MOVEMENT) {
       E.res[0] = 2 * (int)(lc & 7u);
       E.res[1] = 2 * (int)((lc >> 3) & 7u);
@@ -1001,7 +1003,7 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
     }
     deck_activate(E, pc, p, (int)a_play - 1, lane);
   } else if (a_special) { /* Player::play_special src/player.cpp:71-79 */
-    const u32 lc = bcast(LANE_CONST[lane], (int)a_special);
+    const u32 lc = bcast(E.lc, (int)a_special);
     if ((lc >> 9) & 1u) deck_remove_immediate(E, pc, p, (int)a_special - 1, lane);
     else deck_play_immediate(E, pc, p, (int)a_special - 1, lane);
     special = (int)((lc >> 10) & 7u);
@@ -1029,7 +1031,7 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
         card = shop_get(E, idx, lane); /* Shop::transmit */
       } else {
         card = shop_buy(E, idx, lane);
-        E.res[2] -= 2 * (int)((bcast(LANE_CONST[lane], card + 1) >> 13) & 7u); /* Player::pay */
+        E.res[2] -= 2 * (int)((bcast(E.lc, card + 1) >> 13) & 7u); /* Player::pay */
         env_cycle_phase(E);
       }
       if (lane == card + 1) E.discard = addb(E.discard, p, 1); /* Deck::add */
@@ -1059,7 +1061,8 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
   }
 
   /* maybe_end_turn :244-250 */
-  if ((pf & PFL_WON) || E.phase == PH_INACTIVE) env_next_agent(E, pc, p, prm.n_players, lane);
+  const bool turn_ends = (pf & PFL_WON) || E.phase == PH_INACTIVE;
+  if (turn_ends) env_next_agent(E, pc, p, prm.n_players, lane);
   if (lane == p) { E.pf = pf; E.pc = pc; }
   const int agent = (int)E.agent;
   env_update_observation(E, agent, lane);
@@ -1101,8 +1104,11 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
     if (lane == p) { E.pf = pf; E.pc = pc; }
   } else {
     /* Map::player_done src/map.cpp:407-410 for the NEW current agent, or truncation */
-    const u32 here = bcast(getb(E.nbr, agent), 0);
-    if (COG_UNLIKELY(hex_end(here) || E.turn >= prm.max_steps)) {
+    /* the current agent can only have ARRIVED on an end hex by moving or by the turn
+     * passing to a player who already stands on one */
+    bool finished = E.turn >= prm.max_steps;
+    if (!finished && (turn_ends || a_move)) finished = hex_end(bcast(getb(E.nbr, agent), 0));
+    if (COG_UNLIKELY(finished)) {
       done = 1;
       const u32 np = prm.n_players < 4 ? prm.n_players : 4;
       const bool won = lane < 4 && (E.pf & PFL_WON);

@@ -31,6 +31,7 @@ __global__ void k_init(Buffers B, u64 n) {
   E.draw = E.hand = E.active = E.played = E.discard = 0;
   E.shop = (lane >= 1 && lane <= 18) ? 3u : 0u;
   E.nbr = 0;
+  E.lc = LANE_CONST[lane];
   E.pf = E.pc = E.pmv = E.ploc = 0;
   E.Pplay = E.Pspec = E.Prem = 1u;
   E.Pms = 1u | (1u << 7);
