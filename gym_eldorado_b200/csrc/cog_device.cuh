@@ -343,7 +343,8 @@ __device__ __forceinline__ void export_mask(u8 *dst, u32 play, u32 spec, u32 rem
 __device__ __forceinline__ void export_dynamic(const Env &E, const Buffers &B, u64 i, u32 pmask, int lane) {
   u8 *obs = B.obs + i * COGL_OBS_SIZE;
   if (lane == 0) obs[COGL_OBS_PHASE] = (u8)E.phase;
-  if (lane < 3) reinterpret_cast<float *>(obs + COGL_OBS_RES)[lane] = 0.5f * (float)E.res[lane];
+  if (lane < 3) /* no dynamic indexing of E.res: that would push the array to local memory */
+    reinterpret_cast<float *>(obs + COGL_OBS_RES)[lane] = 0.5f * (float)(lane == 0 ? E.res[0] : lane == 1 ? E.res[1] : E.res[2]);
   if (lane >= 1 && lane <= 18) obs[COGL_OBS_SHOP + lane - 1] = (u8)(E.shop & 0xffu);
   for (int p = 0; p < 4; ++p) {
     if (!((pmask >> p) & 1u)) continue;

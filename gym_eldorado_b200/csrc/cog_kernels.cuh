@@ -64,10 +64,10 @@ __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed)
  *                registers for k_steps x {sample; step}, then writes it back once.
  *                `srng` is the sampler's RNG array, `actions` receives the last action. */
 #ifndef COG_MIN_BLOCKS
-#define COG_MIN_BLOCKS 8
+#define COG_MIN_BLOCKS 7
 #endif
 template <bool FUSED>
-__global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step(Buffers B, Params prm, u64 n, const u8 *__restrict__ actions_in, u32 *srng,
+__global__ void __launch_bounds__(BLOCK_THREADS, FUSED ? COG_MIN_BLOCKS : 6) k_step(Buffers B, Params prm, u64 n, const u8 *__restrict__ actions_in, u32 *srng,
                        u8 *actions_out, u64 k_steps) {
   const int lane = threadIdx.x & 31;
   const u64 warp0 = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
