@@ -112,14 +112,20 @@ __device__ __forceinline__ u32 warp_incl_scan(u32 v, int lane) {
   }
   return v;
 }
-/* byte p of a word, as one PRMT each: the selector is a constant when p is, and is
- * computed once per step (common subexpression) when p is the current player */
-__device__ __forceinline__ u32 getb(u32 w, int p) { return __byte_perm(w, 0u, 0x4440u | (u32)p); }
+/* byte p of a word.  Written with shifts and masks so that a literal p (almost always 0,
+ * see "rotated player order" below) folds to one LOP3 / one IADD + one LOP3 */
+__device__ __forceinline__ u32 getb(u32 w, int p) { return (w >> (8 * p)) & 0xffu; }
 __device__ __forceinline__ u32 setb(u32 w, int p, u32 v) {
-  return __byte_perm(w, v, 0x3210u + ((4u - (u32)p) << (4 * p)));
+  const u32 m = 0xffu << (8 * p);
+  return (w & ~m) | ((v << (8 * p)) & m);
 }
 /* u8 arithmetic inside byte p (wraps like the reference's u_char counters) */
-__device__ __forceinline__ u32 addb(u32 w, int p, int d) { return setb(w, p, getb(w, p) + (u32)d); }
+__device__ __forceinline__ u32 addb(u32 w, int p, int d) {
+  const u32 m = 0xffu << (8 * p);
+  return (w & ~m) | ((w + ((u32)d << (8 * p))) & m);
+}
+/* rotate the four bytes of w right by r positions: byte r moves to byte 0 */
+__device__ __forceinline__ u32 rotb(u32 w, u32 r) { return __funnelshift_r(w, w, 8u * r); }
 __device__ __forceinline__ u32 setbit(u32 w, int b, bool v) {
   return (w & ~(1u << b)) | ((u32)v << b);
 }
@@ -227,21 +233,40 @@ struct Buffers {
   int *err;      /* [0] first error code, [1] env index */
 };
 
+/* ROTATED PLAYER ORDER.  The seven words that hold one byte per player (the five piles,
+ * the neighbour cache and info_steps) are kept — in registers and in the hidden record —
+ * rotated by the current agent: byte r belongs to player (agent + r) & 3.  The player whose
+ * turn it is therefore always sits in byte 0, every pile update of the hot path addresses a
+ * literal byte, and the rotation is paid once per turn change (seven funnel shifts).
+ * Functions below take `rp` = a player's RELATIVE byte index, rel(E, p). */
 struct Env {
-  /* lane l <-> card type l-1; byte p = player p */
+  /* lane l <-> card type l-1; byte r = player (agent + r) & 3 */
   u32 draw, hand, active, played, discard;
   u32 shop; /* lane l <-> slot l-1: bits 0-7 stock, bit 8 in_market */
-  u32 nbr;  /* lane d <-> direction d: byte p = hex code next to player p */
+  u32 nbr;  /* lane d <-> direction d: byte r = hex code next to player (agent + r) & 3 */
   u32 lc;   /* LANE_CONST[lane]: card / shop-slot constants of this lane (not stored) */
   /* lane p <-> player p */
   u32 pf, pc, pmv, ploc, Pplay, Pspec, Prem, Pms;
   /* warp-uniform */
-  u32 rng, turn, agent, phase, n_in_market, info_steps;
+  u32 rng, turn, agent, phase, n_in_market;
+  u32 info_steps; /* Info.agent_infos[k].steps_taken, rotated like the piles */
   u32 Splay, Sspec, Srem, Sms;
   int res[3]; /* current_resources * 2 */
   int minx, miny;
 };
 
+__device__ __forceinline__ int rel(const Env &E, int p) { return (p - (int)E.agent) & 3; }
+/* re-base the rotated words after the agent advanced by `r` seats (or, with
+ * r = (4 - agent) & 3, back to absolute player order) */
+__device__ __forceinline__ void env_rotate(Env &E, u32 r) {
+  E.draw = rotb(E.draw, r);
+  E.hand = rotb(E.hand, r);
+  E.active = rotb(E.active, r);
+  E.played = rotb(E.played, r);
+  E.discard = rotb(E.discard, r);
+  E.nbr = rotb(E.nbr, r);
+  E.info_steps = rotb(E.info_steps, r);
+}
 __device__ __forceinline__ int loc_x(u32 w) { return (int)(int16_t)(w & 0xffffu); }
 __device__ __forceinline__ int loc_y(u32 w) { return (int)(int16_t)(w >> 16); }
 __device__ __forceinline__ u32 loc_pack(int x, int y) {
@@ -349,12 +374,13 @@ __device__ __forceinline__ void export_dynamic(const Env &E, const Buffers &B, u
   for (int p = 0; p < 4; ++p) {
     if (!((pmask >> p) & 1u)) continue;
     u8 *pd = obs + COGL_OBS_PLAYER + COGL_PLAYER_STRIDE * p;
+    const int rp = rel(E, p);
     if (lane >= 1 && lane <= 21) {
-      pd[COGL_DK_DRAW + lane - 1] = (u8)getb(E.draw, p);
-      pd[COGL_DK_HAND + lane - 1] = (u8)getb(E.hand, p);
-      pd[COGL_DK_ACTIVE + lane - 1] = (u8)getb(E.active, p);
-      pd[COGL_DK_PLAYED + lane - 1] = (u8)getb(E.played, p);
-      pd[COGL_DK_DISCARD + lane - 1] = (u8)getb(E.discard, p);
+      pd[COGL_DK_DRAW + lane - 1] = (u8)getb(E.draw, rp);
+      pd[COGL_DK_HAND + lane - 1] = (u8)getb(E.hand, rp);
+      pd[COGL_DK_ACTIVE + lane - 1] = (u8)getb(E.active, rp);
+      pd[COGL_DK_PLAYED + lane - 1] = (u8)getb(E.played, rp);
+      pd[COGL_DK_DISCARD + lane - 1] = (u8)getb(E.discard, rp);
     }
     export_mask(pd + COGL_PD_MASK, bcast(E.Pplay, p), bcast(E.Pspec, p), bcast(E.Prem, p),
                 bcast(E.Pms, p), lane);
@@ -363,7 +389,7 @@ __device__ __forceinline__ void export_dynamic(const Env &E, const Buffers &B, u
   if (lane == 0) B.agents[i] = (u8)E.agent;
   if (lane < 4)
     B.infos[i * COGL_INFO_SIZE + COGL_INFO_AGENT + COGL_INFO_AGENT_STRIDE * lane] =
-        (u8)getb(E.info_steps, lane);
+        (u8)getb(E.info_steps, rel(E, lane));
 }
 
 /* ------------------------------------------------------------------- decks */
@@ -388,7 +414,8 @@ __device__ __forceinline__ int pile_pick(u32 pile, int p, u32 target, int lane) 
 }
 
 /* Deck::draw src/cards.cpp:183-211 (with move_discard_to_draw :234-240).
- * `pc` = the player's COG_PF_COUNTS word (uniform copy, updated in place). */
+ * `pc` = the player's COG_PF_COUNTS word (uniform copy, updated in place); here and in
+ * the deck/player functions below `p` is the player's RELATIVE byte index (0 = the agent). */
 __device__ __forceinline__ void deck_draw(Env &E, u32 &pc, int p, u32 n, int lane) {
   u32 n_in_draw = getb(pc, 2);
   if (n_in_draw < n) {
@@ -516,7 +543,7 @@ __device__ __forceinline__ void player_handle_requirement(Env &E, u32 &pf, u32 &
 }
 /* Player::end_turn src/player.cpp:170-180 (+ Deck::discard_all_active/_played
  * src/cards.cpp:219-232); P[p] = S is save_actionmask :166 */
-__device__ __forceinline__ void player_end_turn(Env &E, u32 &pc, int p, int lane) {
+__device__ __forceinline__ void player_end_turn(Env &E, u32 &pc, int p_abs, int p, int lane) {
   pc = setb(pc, 1, 0);
   E.discard = addb(E.discard, p, (int)(getb(E.active, p) + getb(E.played, p)));
   E.active = setb(E.active, p, 0);
@@ -524,7 +551,7 @@ __device__ __forceinline__ void player_end_turn(Env &E, u32 &pc, int p, int lane
   const int n_draw = 4 - (int)getb(pc, 0);
   if (n_draw > 0) deck_draw(E, pc, p, (u32)n_draw, lane);
   res_clear(E);
-  if (lane == p) {
+  if (lane == p_abs) {
     E.Pplay = E.Splay;
     E.Pspec = E.Sspec;
     E.Prem = E.Srem;
@@ -580,17 +607,17 @@ __device__ __forceinline__ void dir_delta(int d, int &dx, int &dy) {
   dx = d == 1 ? 2 : (d == 3 || d == 4) ? -2 : d == 6 ? 2 : 0;
   dy = d == 2 ? 2 : d == 3 ? 2 : (d == 5 || d == 6) ? -2 : 0;
 }
-/* refresh the neighbour cache of player p from the grid (lanes 0..6) */
-__device__ __forceinline__ void nbr_refresh(Env &E, const u8 *__restrict__ grid, int p, int lane) {
-  const u32 loc = bcast(E.ploc, p);
+/* refresh the neighbour cache of player p_abs (relative byte p) from the grid (lanes 0..6) */
+__device__ __forceinline__ void nbr_refresh(Env &E, const u8 *__restrict__ grid, int p_abs, int p, int lane) {
+  const u32 loc = bcast(E.ploc, p_abs);
   int dx, dy;
   dir_delta(lane, dx, dy);
   u32 code = 0;
   if (lane < 7) code = grid_lookup(grid, loc_x(loc) + dx, loc_y(loc) + dy, E.minx, E.miny);
   E.nbr = setb(E.nbr, p, code);
 }
-/* Map::set_movement_mask src/map.cpp:369-387: bits 1..6 of move for `player`,
- * with explicit resources (x2) and active-card count */
+/* Map::set_movement_mask src/map.cpp:369-387: bits 1..6 of move for the player in
+ * relative byte `player`, with explicit resources (x2) and active-card count */
 __device__ __forceinline__ u32 movement_bits(const Env &E, int player, int r0, int r1, int r2,
                                              int n_active, int lane) {
   const u32 c = getb(E.nbr, player);
@@ -603,11 +630,11 @@ __device__ __forceinline__ u32 movement_bits(const Env &E, int player, int r0, i
 
 /* ----------------------------------------------------------------- cog_env */
 /* cog_env::update_observation src/environment.cpp:252-279 */
-__device__ __forceinline__ void env_update_observation(Env &E, int agent, int lane) {
+__device__ __forceinline__ void env_update_observation(Env &E, int agent, int rp, int lane) {
   u32 move = 1u, shop = 1u;
   if (E.phase == PH_MOVEMENT) {
     const int n_active = (int)getb(bcast(E.pc, agent), 1);
-    move |= movement_bits(E, agent, E.res[0], E.res[1], E.res[2], n_active, lane);
+    move |= movement_bits(E, rp, E.res[0], E.res[1], E.res[2], n_active, lane);
   } else if (E.phase == PH_BUYING) {
     shop |= shop_available_bits(E, E.res[2], lane);
   }
@@ -930,6 +957,7 @@ __device__ __forceinline__ void player_reset(Env &E, int p, int lane) {
  * Returns 0 or the error that was reported. */
 __device__ __forceinline__ int env_reset(Env &E, const Params &prm, const Buffers &B, u64 i,
                                          BoardScratch &sc, int lane) {
+  env_rotate(E, (4u - E.agent) & 3u); /* agent 0: relative byte index == player index below */
   E.agent = 0;
   E.phase = PH_INACTIVE;
   BoardState st;
@@ -949,11 +977,11 @@ __device__ __forceinline__ int env_reset(Env &E, const Params &prm, const Buffer
   /* Map::add_players src/map.cpp:343-354: player i stands on hex i of the start piece
    * (defined like that for fewer than 4 players too; SURVEY A#13) */
   if (lane < np) E.ploc = loc_pack(COORDS_LARGE[lane].x, COORDS_LARGE[lane].y);
-  for (int p = 0; p < np; ++p) nbr_refresh(E, grid, p, lane);
+  for (int p = 0; p < np; ++p) nbr_refresh(E, grid, p, p, lane);
   /* Shop::reset src/cards.cpp:94-100 (n_in_market is NOT reset) */
   E.shop = (lane >= 1 && lane <= 18) ? (3u | (((E.lc >> 19) & 1u) << 8)) : 0u;
   E.turn = 0;
-  for (int p = 0; p < np; ++p) env_update_observation(E, p, lane);
+  for (int p = 0; p < np; ++p) env_update_observation(E, p, p, lane);
   E.Splay = bcast(E.Pplay, 0); /* load_actionmask of agent 0 :62-63 */
   E.Sspec = bcast(E.Pspec, 0);
   E.Srem = bcast(E.Prem, 0);
@@ -965,10 +993,15 @@ __device__ __forceinline__ int env_reset(Env &E, const Params &prm, const Buffer
 /* -------------------------------------------------------------------- step */
 /* cog_env::next_agent src/environment.cpp:79-89 */
 __device__ __forceinline__ void env_next_agent(Env &E, u32 &pc, int p, u32 n_players, int lane) {
-  player_end_turn(E, pc, p, lane);
+  player_end_turn(E, pc, p, 0, lane);
   if (lane == p) E.pc = pc;
+  u32 delta = 1; /* seats the agent advances by, mod 4 */
   E.agent = E.agent + 1;
-  if (E.agent >= n_players) E.agent = 0;
+  if (E.agent >= n_players) {
+    E.agent = 0;
+    delta = (4u - (u32)p) & 3u;
+  }
+  env_rotate(E, delta);
   E.Splay = bcast(E.Pplay, (int)E.agent); /* load_actionmask */
   E.Sspec = bcast(E.Pspec, (int)E.agent);
   E.Srem = bcast(E.Prem, (int)E.agent);
@@ -980,16 +1013,24 @@ __device__ __forceinline__ void env_next_agent(Env &E, u32 &pc, int p, u32 n_pla
 /* cog_env::step src/environment.cpp:91-224 followed by vec_cog_env::step_single's
  * auto-reset (include/vec_environment.h:53-61).  `act` = the five ActionData bytes
  * packed play | special<<8 | remove<<16 | move<<24, shop separately.
- * Returns: bit0 done, bits 8-11 players whose exported records changed. */
+ * Returns: bit0 done, bits 8-11 players whose exported records changed.
+ *
+ * LAZY (the fused kernel): update_observation is a pure function of the state the step
+ * leaves behind and its result (P[agent].move / .get_from_shop) is only ever read by a
+ * special action of the same step or by the export after the last step — every other value
+ * is overwritten by the next step's update or by save_actionmask at the end of the turn.
+ * So it is run only when a special action needs it; otherwise `obs_pending` is raised and
+ * the caller runs it once after its last step. */
+template <bool LAZY>
 __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Params &prm, const Buffers &B,
-                                        u64 i, BoardScratch &sc, int lane) {
+                                        u64 i, BoardScratch &sc, bool &obs_pending, int lane) {
   const u32 a_play = act & 0xffu, a_special = (act >> 8) & 0xffu, a_remove = (act >> 16) & 0xffu,
             a_move = act >> 24;
-  const int p = (int)E.agent;
-  E.info_steps = addb(E.info_steps, p, 1); /* info.agent_infos[agent].steps_taken++ :97 */
+  const int p = (int)E.agent; /* relative byte 0 until the agent advances */
+  E.info_steps = addb(E.info_steps, 0, 1); /* info.agent_infos[agent].steps_taken++ :97 */
   if (E.phase == PH_INACTIVE) env_cycle_phase(E);
   u32 pf = bcast(E.pf, p), pc = bcast(E.pc, p);
-  pf = setb(pf, 3, getb(pf, 3) + 1); /* Player::steps_taken */
+  pf += 1u << 24; /* Player::steps_taken (byte 3, wraps) */
   int special = SP_NONE;
 
   if (a_play) { /* Player::play_card src/player.cpp:47-69 */
@@ -1002,24 +1043,24 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
       const int coin = (int)((lc >> 6) & 7u);
       E.res[2] += coin > 0 ? 2 * coin : 1;
     }
-    deck_activate(E, pc, p, (int)a_play - 1, lane);
+    deck_activate(E, pc, 0, (int)a_play - 1, lane);
   } else if (a_special) { /* Player::play_special src/player.cpp:71-79 */
     const u32 lc = bcast(E.lc, (int)a_special);
-    if ((lc >> 9) & 1u) deck_remove_immediate(E, pc, p, (int)a_special - 1, lane);
-    else deck_play_immediate(E, pc, p, (int)a_special - 1, lane);
+    if ((lc >> 9) & 1u) deck_remove_immediate(E, pc, 0, (int)a_special - 1, lane);
+    else deck_play_immediate(E, pc, 0, (int)a_special - 1, lane);
     special = (int)((lc >> 10) & 7u);
   } else if (a_move) { /* Map::move_in_direction src/map.cpp:356-367 */
-    const u32 c = bcast(getb(E.nbr, p), (int)a_move);
+    const u32 c = bcast(getb(E.nbr, 0), (int)a_move);
     int dx, dy;
     dir_delta((int)a_move, dx, dy);
     const u32 loc = bcast(E.ploc, p);
     if (lane == p) E.ploc = loc_pack(loc_x(loc) + dx, loc_y(loc) + dy);
-    nbr_refresh(E, B.grid + i * COGL_GRID_BYTES, p, lane);
+    nbr_refresh(E, B.grid + i * COGL_GRID_BYTES, p, 0, lane);
     if (!(pf & PFL_MOVE_FREE)) {
-      player_handle_requirement(E, pf, pc, p, hex_req(c), (u32)hex_n(c), lane);
+      player_handle_requirement(E, pf, pc, 0, hex_req(c), (u32)hex_n(c), lane);
     } else {
       pf &= ~(u32)PFL_MOVE_FREE;
-      player_enable_playing(E, p, lane);
+      player_enable_playing(E, 0, lane);
     }
     if (lane == p) E.pmv++;
     pf = (pf & ~(u32)PFL_WON) | (u32)hex_end(c);
@@ -1035,24 +1076,24 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
         E.res[2] -= 2 * (int)((bcast(E.lc, card + 1) >> 13) & 7u); /* Player::pay */
         env_cycle_phase(E);
       }
-      if (lane == card + 1) E.discard = addb(E.discard, p, 1); /* Deck::add */
+      if (lane == card + 1) E.discard = addb(E.discard, 0, 1); /* Deck::add */
       pf = setb(pf, 2, getb(pf, 2) + 1);
     } else if (a_remove) {
-      deck_remove_immediate(E, pc, p, (int)a_remove - 1, lane);
+      deck_remove_immediate(E, pc, 0, (int)a_remove - 1, lane);
       const u32 nr = (getb(pf, 1) - 1u) & 0xffu;
       pf = setb(pf, 1, nr);
-      if (!nr) player_enable_playing(E, p, lane);
+      if (!nr) player_enable_playing(E, 0, lane);
       else special = SP_REMOVE_PENDING;
     } else {
       env_cycle_phase(E);
       if (getb(pf, 1) > 0) {
         pf = setb(pf, 1, 0);
-        player_enable_playing(E, p, lane);
+        player_enable_playing(E, 0, lane);
       }
     }
     if (pf & PFL_CARD_FREE) {
       pf &= ~(u32)PFL_CARD_FREE;
-      player_enable_playing(E, p, lane);
+      player_enable_playing(E, 0, lane);
     }
   }
 
@@ -1066,11 +1107,13 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
   if (turn_ends) env_next_agent(E, pc, p, prm.n_players, lane);
   if (lane == p) { E.pf = pf; E.pc = pc; }
   const int agent = (int)E.agent;
-  env_update_observation(E, agent, lane);
-  u32 touched = (1u << p) | (1u << agent);
+  u32 touched = LAZY ? 0xfu : (1u << p) | (1u << agent);
   u32 done = 0;
 
   if (COG_UNLIKELY(special != SP_NONE)) { /* :183-186; src/cards.cpp:8-36; remove lambda :156-158 */
+    env_update_observation(E, agent, 0, lane);
+    obs_pending = false;
+    const int rp = rel(E, p); /* the player who acted; the agent may have advanced */
     u32 Pms = bcast(E.Pms, agent);
     switch (special) {
     case SP_TRANSMIT: /* transmit_action */
@@ -1078,12 +1121,12 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
       player_disable_playing(E);
       pf |= PFL_CARD_FREE;
       break;
-    case SP_DRAW2: deck_draw(E, pc, p, 2, lane); break;
-    case SP_DRAW3: deck_draw(E, pc, p, 3, lane); break;
+    case SP_DRAW2: deck_draw(E, pc, rp, 2, lane); break;
+    case SP_DRAW3: deck_draw(E, pc, rp, 3, lane); break;
     case SP_DRAW1_REMOVE1:
     case SP_DRAW2_REMOVE2: { /* draw_and_remove_action<n, m> */
       const u32 k = special == SP_DRAW1_REMOVE1 ? 1u : 2u;
-      deck_draw(E, pc, p, k, lane);
+      deck_draw(E, pc, rp, k, lane);
       pf = setb(pf, 1, k);
       if (lane == agent) E.Prem = E.Pplay; /* P.remove = (stale) P.play */
       player_disable_playing(E);
@@ -1091,7 +1134,7 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
       break;
     }
     case SP_NATIVE: { /* native_action: any passable neighbour of the PLAYER who played it */
-      const u32 mv = movement_bits(E, p, 200, 200, 200, 100, lane);
+      const u32 mv = movement_bits(E, rp, 200, 200, 200, 100, lane);
       Pms = (Pms & 1u) | mv | (((Pms >> 7) & 1u) << 7);
       pf |= PFL_MOVE_FREE;
       player_disable_playing(E);
@@ -1104,13 +1147,18 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
     if (lane == agent) E.Pms = Pms;
     if (lane == p) { E.pf = pf; E.pc = pc; }
   } else {
-    /* Map::player_done src/map.cpp:407-410 for the NEW current agent, or truncation */
-    /* the current agent can only have ARRIVED on an end hex by moving or by the turn
+    if (LAZY) obs_pending = true;
+    else env_update_observation(E, agent, 0, lane);
+    /* Map::player_done src/map.cpp:407-410 for the NEW current agent, or truncation.
+     * The current agent can only have ARRIVED on an end hex by moving or by the turn
      * passing to a player who already stands on one */
     bool finished = E.turn >= prm.max_steps;
-    if (!finished && (turn_ends || a_move)) finished = hex_end(bcast(getb(E.nbr, agent), 0));
+    if (turn_ends || a_move) finished = finished || hex_end(bcast(getb(E.nbr, 0), 0));
     if (COG_UNLIKELY(finished)) {
       done = 1;
+      obs_pending = false;
+      env_rotate(E, (4u - E.agent) & 3u); /* absolute player order for the bookkeeping below */
+      E.agent = 0;
       const u32 np = prm.n_players < 4 ? prm.n_players : 4;
       const bool won = lane < 4 && (E.pf & PFL_WON);
       const u32 winners = __ballot_sync(COG_FULL, won); /* get_reward :281-288 sums all 4 slots */

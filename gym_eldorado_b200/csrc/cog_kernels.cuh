@@ -81,11 +81,13 @@ __global__ void __launch_bounds__(BLOCK_THREADS, FUSED ? COG_MIN_BLOCKS : 6) k_s
     if (FUSED) {
       u32 sr = srng[i];
       u32 act = 0, a_shop = 0, touched = 0;
+      bool obs_pending = false;
       for (u32 k = 0; k < (u32)k_steps; ++k) {
         sample_action(sr, E.Splay, E.Sspec, E.Srem, E.Sms, act, a_shop);
-        status = env_step(E, act, a_shop, prm, B, i, sc, lane);
+        status = env_step<true>(E, act, a_shop, prm, B, i, sc, obs_pending, lane);
         touched |= status >> 8;
       }
+      if (obs_pending) env_update_observation(E, (int)E.agent, 0, lane);
       __syncwarp(); /* every lane has read srng[i] before lane 0 overwrites it */
       if (lane == 0) srng[i] = sr;
       if (k_steps) {
@@ -98,7 +100,8 @@ __global__ void __launch_bounds__(BLOCK_THREADS, FUSED ? COG_MIN_BLOCKS : 6) k_s
       const u8 *a = actions_in + i * COGL_ACTION_SIZE;
       const u32 mine = lane < 5 ? (u32)a[lane] : 0u;
       const u32 act = bcast(mine, 0) | (bcast(mine, 1) << 8) | (bcast(mine, 2) << 16) | (bcast(mine, 3) << 24);
-      status = env_step(E, act, bcast(mine, 4), prm, B, i, sc, lane);
+      bool obs_pending = false;
+      status = env_step<false>(E, act, bcast(mine, 4), prm, B, i, sc, obs_pending, lane);
       steps_done += 1;
     }
     env_store(E, B.hidden + i * COG_HID_WORDS, lane);

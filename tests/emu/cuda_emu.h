@@ -217,6 +217,9 @@ static inline unsigned __byte_perm(unsigned a, unsigned b, unsigned sel) {
   return r;
 }
 static inline unsigned __umulhi(unsigned a, unsigned b) { return (unsigned)(((uint64_t)a * b) >> 32); }
+static inline unsigned __funnelshift_r(unsigned lo, unsigned hi, unsigned s) {
+  return (unsigned)(((((uint64_t)hi) << 32) | lo) >> (s & 31u));
+}
 
 /* lanes run one at a time, so plain read-modify-write is atomic */
 template <class T> static inline T atomicOr(T *p, T v) { T o = *p; *p = o | v; return o; }
