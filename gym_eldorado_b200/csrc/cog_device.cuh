@@ -31,6 +31,11 @@ typedef uint64_t u64;
  * rejections) out of the hot instruction stream */
 #define COG_UNLIKELY(x) __builtin_expect(!!(x), 0)
 #define COG_LIKELY(x) __builtin_expect(!!(x), 1)
+#ifdef COG_EMU /* host build of tests/emu: libstdc++ itself spells __attribute__((__noinline__)) */
+#define COG_NOINLINE __attribute__((noinline))
+#else
+#define COG_NOINLINE __noinline__
+#endif
 
 /* ------------------------------------------------------------------ tables */
 struct card_def { u8 cost, market, single, res0, res1, res2, special; };
@@ -245,16 +250,23 @@ struct Env {
   u32 shop; /* lane l <-> slot l-1: bits 0-7 stock, bit 8 in_market */
   u32 nbr;  /* lane d <-> direction d: byte r = hex code next to player (agent + r) & 3 */
   u32 lc;   /* LANE_CONST[lane]: card / shop-slot constants of this lane (not stored) */
-  /* lane p <-> player p */
-  u32 pf, pc, pmv, ploc, Pplay, Pspec, Prem, Pms;
+  /* lane p <-> player p.  pf / pc of the CURRENT agent are stale here: the live copies
+   * are the uniform cpf / cpc below (written back when the turn passes on) */
+  u32 pf, pc, pmv, ploc, Pplay, Prem, Pms;
   /* warp-uniform */
   u32 rng, turn, agent, phase, n_in_market;
+  u32 cpf, cpc;   /* COG_PF_FLAGS / COG_PF_COUNTS words of the current agent */
   u32 info_steps; /* Info.agent_infos[k].steps_taken, rotated like the piles */
-  u32 Splay, Sspec, Srem, Sms;
+  /* S = selected_action_masks.  play_special is not stored: in S and in every P[p] it equals
+   * play & (special cards | bit 0) — each writer of the reference sets play_special[k] =
+   * play[k] && is_special(k - 1) and both [0] are always true (src/cards.cpp:183-290,
+   * src/player.cpp:191-206, include/api.h:104-118) */
+  u32 Splay, Srem, Sms;
   int res[3]; /* current_resources * 2 */
   int minx, miny;
 };
 
+__device__ __forceinline__ u32 spec_of(u32 play) { return play & (COG_SPECIAL_MASK | 1u); }
 __device__ __forceinline__ int rel(const Env &E, int p) { return (p - (int)E.agent) & 3; }
 /* re-base the rotated words after the agent advanced by `r` seats (or, with
  * r = (4 - agent) & 3, back to absolute player order) */
@@ -290,7 +302,6 @@ __device__ __forceinline__ void env_load(Env &E, const u32 *__restrict__ rec, in
   E.pmv = bcast(pw, 4 * COG_PF_MOVES + q);
   E.ploc = bcast(pw, 4 * COG_PF_LOC + q);
   E.Pplay = bcast(pw, 4 * COG_PF_MPLAY + q);
-  E.Pspec = bcast(pw, 4 * COG_PF_MSPEC + q);
   E.Prem = bcast(pw, 4 * COG_PF_MREM + q);
   E.Pms = bcast(pw, 4 * COG_PF_MMS + q);
   E.rng = bcast(ew, COG_ES_RNG);
@@ -306,10 +317,11 @@ __device__ __forceinline__ void env_load(Env &E, const u32 *__restrict__ rec, in
   E.minx = loc_x(mn);
   E.miny = loc_y(mn);
   E.Splay = bcast(ew, COG_ES_SPLAY);
-  E.Sspec = bcast(ew, COG_ES_SSPEC);
   E.Srem = bcast(ew, COG_ES_SREM);
   E.Sms = bcast(ew, COG_ES_SMS);
   E.info_steps = bcast(ew, COG_ES_INFOSTEPS);
+  E.cpf = bcast(ew, COG_ES_CPF);
+  E.cpc = bcast(ew, COG_ES_CPC);
 }
 
 __device__ __forceinline__ void env_store(const Env &E, u32 *__restrict__ rec, int lane) {
@@ -328,7 +340,6 @@ __device__ __forceinline__ void env_store(const Env &E, u32 *__restrict__ rec, i
   t = bcast(E.pmv, q);   if (f == COG_PF_MOVES) pw = t;
   t = bcast(E.ploc, q);  if (f == COG_PF_LOC) pw = t;
   t = bcast(E.Pplay, q); if (f == COG_PF_MPLAY) pw = t;
-  t = bcast(E.Pspec, q); if (f == COG_PF_MSPEC) pw = t;
   t = bcast(E.Prem, q);  if (f == COG_PF_MREM) pw = t;
   t = bcast(E.Pms, q);   if (f == COG_PF_MMS) pw = t;
   rec[COG_HL_PLAYER * 32 + lane] = pw;
@@ -342,10 +353,11 @@ __device__ __forceinline__ void env_store(const Env &E, u32 *__restrict__ rec, i
   case COG_ES_RES2: ew = (u32)E.res[2]; break;
   case COG_ES_MIN: ew = loc_pack(E.minx, E.miny); break;
   case COG_ES_SPLAY: ew = E.Splay; break;
-  case COG_ES_SSPEC: ew = E.Sspec; break;
   case COG_ES_SREM: ew = E.Srem; break;
   case COG_ES_SMS: ew = E.Sms; break;
   case COG_ES_INFOSTEPS: ew = E.info_steps; break;
+  case COG_ES_CPF: ew = E.cpf; break;
+  case COG_ES_CPC: ew = E.cpc; break;
   default: break;
   }
   rec[COG_HL_ENV * 32 + lane] = ew;
@@ -382,10 +394,10 @@ __device__ __forceinline__ void export_dynamic(const Env &E, const Buffers &B, u
       pd[COGL_DK_PLAYED + lane - 1] = (u8)getb(E.played, rp);
       pd[COGL_DK_DISCARD + lane - 1] = (u8)getb(E.discard, rp);
     }
-    export_mask(pd + COGL_PD_MASK, bcast(E.Pplay, p), bcast(E.Pspec, p), bcast(E.Prem, p),
-                bcast(E.Pms, p), lane);
+    const u32 Pplay = bcast(E.Pplay, p);
+    export_mask(pd + COGL_PD_MASK, Pplay, spec_of(Pplay), bcast(E.Prem, p), bcast(E.Pms, p), lane);
   }
-  export_mask(B.masks + i * COGL_MASK_SIZE, E.Splay, E.Sspec, E.Srem, E.Sms, lane);
+  export_mask(B.masks + i * COGL_MASK_SIZE, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, lane);
   if (lane == 0) B.agents[i] = (u8)E.agent;
   if (lane < 4)
     B.infos[i * COGL_INFO_SIZE + COGL_INFO_AGENT + COGL_INFO_AGENT_STRIDE * lane] =
@@ -434,7 +446,6 @@ __device__ __forceinline__ void deck_draw(Env &E, u32 &pc, int p, u32 n, int lan
         E.hand = addb(E.hand, p, 1);
       }
       E.Splay |= 1u << cl;
-      E.Sspec = (E.Sspec & ~(1u << cl)) | (COG_SPECIAL_MASK & (1u << cl));
     }
     n_in_draw = (n_in_draw - 1) & 0xffu;
   }
@@ -453,9 +464,7 @@ __device__ __forceinline__ void deck_activate(Env &E, u32 &pc, int p, int idx, i
     E.hand = addb(E.hand, p, -1);
     E.active = addb(E.active, p, 1);
   }
-  const bool still = prev > 1;
-  E.Splay = setbit(E.Splay, cl, still);
-  E.Sspec = setbit(E.Sspec, cl, still && ((COG_SPECIAL_MASK >> cl) & 1u));
+  E.Splay = setbit(E.Splay, cl, prev > 1);
 }
 /* Deck::play_last_activated src/cards.cpp:255-261 */
 __device__ __forceinline__ void deck_play_last_activated(Env &E, u32 &pc, int p, int lane) {
@@ -475,9 +484,7 @@ __device__ __forceinline__ void deck_play_immediate(Env &E, u32 &pc, int p, int 
     E.hand = addb(E.hand, p, -1);
     E.played = addb(E.played, p, 1);
   }
-  const bool still = prev > 1;
-  E.Splay = setbit(E.Splay, cl, still);
-  E.Sspec = setbit(E.Sspec, cl, still && ((COG_SPECIAL_MASK >> cl) & 1u));
+  E.Splay = setbit(E.Splay, cl, prev > 1);
 }
 /* Deck::remove_immediate src/cards.cpp:281-290 */
 __device__ __forceinline__ void deck_remove_immediate(Env &E, u32 &pc, int p, int idx, int lane) {
@@ -487,23 +494,19 @@ __device__ __forceinline__ void deck_remove_immediate(Env &E, u32 &pc, int p, in
   if (lane == cl) E.hand = addb(E.hand, p, -1);
   const bool still = prev > 1;
   E.Srem = setbit(E.Srem, cl, ((E.Srem >> cl) & 1u) && still);
-  const bool play = ((E.Splay >> cl) & 1u) && still;
-  E.Splay = setbit(E.Splay, cl, play);
-  E.Sspec = setbit(E.Sspec, cl, play && ((COG_SPECIAL_MASK >> cl) & 1u));
+  if (!still) E.Splay &= ~(1u << cl);
 }
 
 /* ------------------------------------------------------------------ player */
 /* Player::disable_playing src/player.cpp:191-196 */
 __device__ __forceinline__ void player_disable_playing(Env &E) {
   E.Splay = 1u;
-  E.Sspec = 1u;
 }
 /* Player::enable_playing src/player.cpp:198-206: play[k] = hand[k-1] > 0 is one ballot */
 __device__ __forceinline__ void player_enable_playing(Env &E, int p, int lane) {
   E.Srem = 1u;
   const u32 have = __ballot_sync(COG_FULL, lane >= 1 && lane <= 21 && getb(E.hand, p) > 0);
   E.Splay = (E.Splay & 1u) | have;
-  E.Sspec = (E.Sspec & 1u) | (have & COG_SPECIAL_MASK);
 }
 /* Player::discard_cards src/player.cpp:85-104 (no clamp) / remove_cards :106-131 (clamped) */
 __device__ __forceinline__ void player_drop_active(Env &E, u32 &pc, int p, u32 n, bool remove, int lane) {
@@ -553,7 +556,6 @@ __device__ __forceinline__ void player_end_turn(Env &E, u32 &pc, int p_abs, int 
   res_clear(E);
   if (lane == p_abs) {
     E.Pplay = E.Splay;
-    E.Pspec = E.Sspec;
     E.Prem = E.Srem;
     E.Pms = E.Sms;
   }
@@ -630,10 +632,11 @@ __device__ __forceinline__ u32 movement_bits(const Env &E, int player, int r0, i
 
 /* ----------------------------------------------------------------- cog_env */
 /* cog_env::update_observation src/environment.cpp:252-279 */
-__device__ __forceinline__ void env_update_observation(Env &E, int agent, int rp, int lane) {
+/* `pc` = the COG_PF_COUNTS word of player `agent` (relative byte rp) */
+__device__ __forceinline__ void env_update_observation(Env &E, int agent, int rp, u32 pc, int lane) {
   u32 move = 1u, shop = 1u;
   if (E.phase == PH_MOVEMENT) {
-    const int n_active = (int)getb(bcast(E.pc, agent), 1);
+    const int n_active = (int)getb(pc, 1);
     move |= movement_bits(E, rp, E.res[0], E.res[1], E.res[2], n_active, lane);
   } else if (E.phase == PH_BUYING) {
     shop |= shop_available_bits(E, E.res[2], lane);
@@ -930,6 +933,16 @@ __device__ __forceinline__ int bg_finalize(const BoardScratch &sc, const BoardSt
 }
 
 /* ------------------------------------------------------------------- reset */
+/* back to absolute player order with agent 0: the current agent's flag / count words go
+ * back to its lane, the rotated words are re-based, cpf / cpc follow player 0 */
+__device__ __forceinline__ void env_to_absolute(Env &E, int lane) {
+  if (lane == (int)E.agent) { E.pf = E.cpf; E.pc = E.cpc; }
+  env_rotate(E, (4u - E.agent) & 3u);
+  E.agent = 0;
+  E.cpf = bcast(E.pf, 0);
+  E.cpc = bcast(E.pc, 0);
+}
+
 __device__ __forceinline__ void report_error(const Buffers &B, int code, u64 i, int lane) {
   if (lane == 0 && atomicCAS(&B.err[0], 0, code) == 0) B.err[1] = (int)i;
 }
@@ -943,12 +956,12 @@ __device__ __forceinline__ void player_reset(Env &E, int p, int lane) {
   E.hand = setb(E.hand, p, 0);
   E.active = setb(E.active, p, 0);
   E.discard = setb(E.discard, p, lane == 1 ? 3u : lane == 8 ? 4u : lane == 6 ? 1u : 0u);
-  E.Splay = 1u; E.Srem = 1u; E.Sspec = 1u;
+  E.Splay = 1u; E.Srem = 1u;
   E.Sms |= 1u | (1u << 7);
   deck_draw(E, pc, p, 4, lane);
   if (lane == p) {
     E.pf = 0; E.pmv = 0; E.pc = pc;
-    E.Pplay = E.Splay; E.Pspec = E.Sspec; E.Prem = E.Srem; E.Pms = E.Sms; /* save_actionmask */
+    E.Pplay = E.Splay; E.Prem = E.Srem; E.Pms = E.Sms; /* save_actionmask */
   }
 }
 
@@ -957,8 +970,7 @@ __device__ __forceinline__ void player_reset(Env &E, int p, int lane) {
  * Returns 0 or the error that was reported. */
 __device__ __forceinline__ int env_reset(Env &E, const Params &prm, const Buffers &B, u64 i,
                                          BoardScratch &sc, int lane) {
-  env_rotate(E, (4u - E.agent) & 3u); /* agent 0: relative byte index == player index below */
-  E.agent = 0;
+  env_to_absolute(E, lane); /* agent 0: relative byte index == player index below */
   E.phase = PH_INACTIVE;
   BoardState st;
   bg_map_reset(sc, st, lane);
@@ -981,20 +993,28 @@ __device__ __forceinline__ int env_reset(Env &E, const Params &prm, const Buffer
   /* Shop::reset src/cards.cpp:94-100 (n_in_market is NOT reset) */
   E.shop = (lane >= 1 && lane <= 18) ? (3u | (((E.lc >> 19) & 1u) << 8)) : 0u;
   E.turn = 0;
-  for (int p = 0; p < np; ++p) env_update_observation(E, p, p, lane);
+  for (int p = 0; p < np; ++p) env_update_observation(E, p, p, bcast(E.pc, p), lane);
   E.Splay = bcast(E.Pplay, 0); /* load_actionmask of agent 0 :62-63 */
-  E.Sspec = bcast(E.Pspec, 0);
   E.Srem = bcast(E.Prem, 0);
   E.Sms = bcast(E.Pms, 0);
+  E.cpf = bcast(E.pf, 0);
+  E.cpc = bcast(E.pc, 0);
   if (lane == 0) atomicAdd(&B.stats[10 /* COG_STAT_RESETS */], 1ull);
   return 0;
+}
+/* Out-of-line copy for the step kernels: episode ends are rare, and keeping board
+ * generation out of the step loop's instruction stream (and register allocation) matters
+ * more than the call.  The caller passes a COPY of its env so that its own stays in registers. */
+__device__ COG_NOINLINE int env_reset_outlined(Env &E, const Params &prm, const Buffers &B, u64 i,
+                                               BoardScratch &sc, int lane) {
+  return env_reset(E, prm, B, i, sc, lane);
 }
 
 /* -------------------------------------------------------------------- step */
 /* cog_env::next_agent src/environment.cpp:79-89 */
-__device__ __forceinline__ void env_next_agent(Env &E, u32 &pc, int p, u32 n_players, int lane) {
+__device__ __forceinline__ void env_next_agent(Env &E, u32 pf, u32 &pc, int p, u32 n_players, int lane) {
   player_end_turn(E, pc, p, 0, lane);
-  if (lane == p) E.pc = pc;
+  if (lane == p) { E.pf = pf; E.pc = pc; } /* the old agent's words return to its lane */
   u32 delta = 1; /* seats the agent advances by, mod 4 */
   E.agent = E.agent + 1;
   if (E.agent >= n_players) {
@@ -1002,8 +1022,9 @@ __device__ __forceinline__ void env_next_agent(Env &E, u32 &pc, int p, u32 n_pla
     delta = (4u - (u32)p) & 3u;
   }
   env_rotate(E, delta);
+  E.cpf = bcast(E.pf, (int)E.agent);
+  E.cpc = bcast(E.pc, (int)E.agent);
   E.Splay = bcast(E.Pplay, (int)E.agent); /* load_actionmask */
-  E.Sspec = bcast(E.Pspec, (int)E.agent);
   E.Srem = bcast(E.Prem, (int)E.agent);
   E.Sms = bcast(E.Pms, (int)E.agent);
   res_clear(E);
@@ -1021,15 +1042,20 @@ __device__ __forceinline__ void env_next_agent(Env &E, u32 &pc, int p, u32 n_pla
  * is overwritten by the next step's update or by save_actionmask at the end of the turn.
  * So it is run only when a special action needs it; otherwise `obs_pending` is raised and
  * the caller runs it once after its last step. */
-template <bool LAZY>
-__device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Params &prm, const Buffers &B,
+template <bool LAZY, bool PLAY_ONLY>
+__device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop_in, const Params &prm, const Buffers &B,
                                         u64 i, BoardScratch &sc, bool &obs_pending, int lane) {
-  const u32 a_play = act & 0xffu, a_special = (act >> 8) & 0xffu, a_remove = (act >> 16) & 0xffu,
-            a_move = act >> 24;
+  /* PLAY_ONLY: the caller knows that only the `play` head can be non-zero (the sampler's
+   * fast path) — every other branch of the step folds away at compile time */
+  const u32 a_play = act & 0xffu;
+  const u32 a_special = PLAY_ONLY ? 0u : (act >> 8) & 0xffu;
+  const u32 a_remove = PLAY_ONLY ? 0u : (act >> 16) & 0xffu;
+  const u32 a_move = PLAY_ONLY ? 0u : act >> 24;
+  const u32 a_shop = PLAY_ONLY ? 0u : a_shop_in;
   const int p = (int)E.agent; /* relative byte 0 until the agent advances */
   E.info_steps = addb(E.info_steps, 0, 1); /* info.agent_infos[agent].steps_taken++ :97 */
   if (E.phase == PH_INACTIVE) env_cycle_phase(E);
-  u32 pf = bcast(E.pf, p), pc = bcast(E.pc, p);
+  u32 pf = E.cpf, pc = E.cpc;
   pf += 1u << 24; /* Player::steps_taken (byte 3, wraps) */
   int special = SP_NONE;
 
@@ -1104,14 +1130,18 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
 
   /* maybe_end_turn :244-250 */
   const bool turn_ends = (pf & PFL_WON) || E.phase == PH_INACTIVE;
-  if (turn_ends) env_next_agent(E, pc, p, prm.n_players, lane);
-  if (lane == p) { E.pf = pf; E.pc = pc; }
+  if (turn_ends) {
+    env_next_agent(E, pf, pc, p, prm.n_players, lane);
+  } else {
+    E.cpf = pf;
+    E.cpc = pc;
+  }
   const int agent = (int)E.agent;
   u32 touched = LAZY ? 0xfu : (1u << p) | (1u << agent);
   u32 done = 0;
 
   if (COG_UNLIKELY(special != SP_NONE)) { /* :183-186; src/cards.cpp:8-36; remove lambda :156-158 */
-    env_update_observation(E, agent, 0, lane);
+    env_update_observation(E, agent, 0, E.cpc, lane);
     obs_pending = false;
     const int rp = rel(E, p); /* the player who acted; the agent may have advanced */
     u32 Pms = bcast(E.Pms, agent);
@@ -1145,10 +1175,16 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
       break;
     }
     if (lane == agent) E.Pms = Pms;
-    if (lane == p) { E.pf = pf; E.pc = pc; }
+    if (p == agent) { /* still this player's turn: the live copies are the uniform ones */
+      E.cpf = pf;
+      E.cpc = pc;
+    } else if (lane == p) {
+      E.pf = pf;
+      E.pc = pc;
+    }
   } else {
     if (LAZY) obs_pending = true;
-    else env_update_observation(E, agent, 0, lane);
+    else env_update_observation(E, agent, 0, E.cpc, lane);
     /* Map::player_done src/map.cpp:407-410 for the NEW current agent, or truncation.
      * The current agent can only have ARRIVED on an end hex by moving or by the turn
      * passing to a player who already stands on one */
@@ -1157,8 +1193,7 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
     if (COG_UNLIKELY(finished)) {
       done = 1;
       obs_pending = false;
-      env_rotate(E, (4u - E.agent) & 3u); /* absolute player order for the bookkeeping below */
-      E.agent = 0;
+      env_to_absolute(E, lane); /* absolute player order for the bookkeeping below */
       const u32 np = prm.n_players < 4 ? prm.n_players : 4;
       const bool won = lane < 4 && (E.pf & PFL_WON);
       const u32 winners = __ballot_sync(COG_FULL, won); /* get_reward :281-288 sums all 4 slots */
@@ -1195,7 +1230,9 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop, const Param
         atomicAdd(&B.stats[9], (unsigned long long)added);
       }
       if (lane < 4 && won) atomicAdd(&B.stats[4 + lane], 1ull);
-      env_reset(E, prm, B, i, sc, lane); /* auto-reset, the RNG stream continues */
+      Env T = E; /* auto-reset, the RNG stream continues */
+      env_reset_outlined(T, prm, B, i, sc, lane);
+      E = T;
       touched = 0xfu;
     }
   }
@@ -1230,22 +1267,24 @@ __device__ __forceinline__ bool minstd_skip4_unit_draws(u32 &s) {
   return true;
 }
 
-__device__ __forceinline__ void sample_action(u32 &rng, u32 play, u32 spec, u32 rem, u32 ms, u32 &act,
+/* The heads are bit sets with nothing above bit 21 (play, special, remove) / bit 25 (ms =
+ * move | get_from_shop << 7): every producer builds them from lane-guarded ballots. */
+/* Returns true when only the `play` head had a choice (act < 256, a_shop = 0). */
+__device__ __forceinline__ bool sample_action(u32 &rng, u32 play, u32 spec, u32 rem, u32 ms, u32 &act,
                                               u32 &a_shop) {
-  const u32 a0 = sample_head(rng, play & 0x3fffffu);
-  spec &= 0x3fffffu;
-  rem &= 0x3fffffu;
-  const u32 mv = ms & 0x7fu, shop = (ms >> 7) & 0x7ffffu;
-  if ((spec | rem | mv | shop) == 1u && (spec & rem & mv & shop) == 1u && minstd_skip4_unit_draws(rng)) {
+  const u32 a0 = sample_head(rng, play);
+  if (spec == 1u && rem == 1u && ms == 0x81u && minstd_skip4_unit_draws(rng)) {
     a_shop = 0; /* the reference's own flow: only `play` ever has a choice (SURVEY A#2) */
     act = a0;
-    return;
+    return true;
   }
+  const u32 mv = ms & 0x7fu, shop = ms >> 7;
   const u32 a1 = sample_head(rng, spec);
   const u32 a2 = sample_head(rng, rem);
   const u32 a3 = sample_head(rng, mv);
   a_shop = sample_head(rng, shop);
   act = a0 | (a1 << 8) | (a2 << 16) | (a3 << 24);
+  return false;
 }
 
 }  // namespace cog

@@ -33,11 +33,12 @@ __global__ void k_init(Buffers B, u64 n) {
   E.nbr = 0;
   E.lc = LANE_CONST[lane];
   E.pf = E.pc = E.pmv = E.ploc = 0;
-  E.Pplay = E.Pspec = E.Prem = 1u;
+  E.cpf = E.cpc = 0;
+  E.Pplay = E.Prem = 1u;
   E.Pms = 1u | (1u << 7);
   E.rng = 1;
   E.turn = 0; E.agent = 0; E.phase = 0; E.n_in_market = 6; E.info_steps = 0;
-  E.Splay = E.Sspec = E.Srem = 1u;
+  E.Splay = E.Srem = 1u;
   E.Sms = 1u | (1u << 7);
   E.res[0] = E.res[1] = E.res[2] = 0;
   E.minx = E.miny = 0;
@@ -64,7 +65,7 @@ __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed)
  *                registers for k_steps x {sample; step}, then writes it back once.
  *                `srng` is the sampler's RNG array, `actions` receives the last action. */
 #ifndef COG_MIN_BLOCKS
-#define COG_MIN_BLOCKS 7
+#define COG_MIN_BLOCKS 8
 #endif
 template <bool FUSED>
 __global__ void __launch_bounds__(BLOCK_THREADS, FUSED ? COG_MIN_BLOCKS : 6) k_step(Buffers B, Params prm, u64 n, const u8 *__restrict__ actions_in, u32 *srng,
@@ -83,11 +84,13 @@ __global__ void __launch_bounds__(BLOCK_THREADS, FUSED ? COG_MIN_BLOCKS : 6) k_s
       u32 act = 0, a_shop = 0, touched = 0;
       bool obs_pending = false;
       for (u32 k = 0; k < (u32)k_steps; ++k) {
-        sample_action(sr, E.Splay, E.Sspec, E.Srem, E.Sms, act, a_shop);
-        status = env_step<true>(E, act, a_shop, prm, B, i, sc, obs_pending, lane);
+        if (sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop))
+          status = env_step<true, true>(E, act, 0, prm, B, i, sc, obs_pending, lane);
+        else
+          status = env_step<true, false>(E, act, a_shop, prm, B, i, sc, obs_pending, lane);
         touched |= status >> 8;
       }
-      if (obs_pending) env_update_observation(E, (int)E.agent, 0, lane);
+      if (obs_pending) env_update_observation(E, (int)E.agent, 0, E.cpc, lane);
       __syncwarp(); /* every lane has read srng[i] before lane 0 overwrites it */
       if (lane == 0) srng[i] = sr;
       if (k_steps) {
@@ -101,7 +104,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, FUSED ? COG_MIN_BLOCKS : 6) k_s
       const u32 mine = lane < 5 ? (u32)a[lane] : 0u;
       const u32 act = bcast(mine, 0) | (bcast(mine, 1) << 8) | (bcast(mine, 2) << 16) | (bcast(mine, 3) << 24);
       bool obs_pending = false;
-      status = env_step<false>(E, act, bcast(mine, 4), prm, B, i, sc, obs_pending, lane);
+      status = env_step<false, false>(E, act, bcast(mine, 4), prm, B, i, sc, obs_pending, lane);
       steps_done += 1;
     }
     env_store(E, B.hidden + i * COG_HID_WORDS, lane);

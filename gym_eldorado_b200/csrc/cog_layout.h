@@ -34,10 +34,11 @@ enum {
 
 /* ---- hidden per-env record ------------------------------------------------
  * line 0..4  card piles draw/hand/active/played/discard: lane l (1..21) holds card
- *            type l-1, byte p of the word = player p's count
+ *            type l-1, one byte per player, ROTATED by the current agent: byte r of the
+ *            word = the count of player (agent + r) & 3 (the agent is always byte 0)
  * line 5     shop: lane l (1..18) holds slot l-1: bits 0-7 n_available, bit 8 in_market
- * line 6     neighbour cache: lane d (0..6): byte p = hex code of the hex in direction d
- *            of player p (d = 0: the hex the player stands on)
+ * line 6     neighbour cache: lane d (0..6): byte r = hex code of the hex in direction d
+ *            of player (agent + r) & 3 (d = 0: the hex the player stands on)
  * line 7     per-player fields, word 4*f + p = field f of player p (COG_PF_*)
  * line 8     env scalars, word = COG_ES_*
  */
@@ -54,7 +55,8 @@ enum {
   COG_PF_COUNTS = 1, /* byte0 n_in_hand, byte1 n_active, byte2 n_in_draw, byte3 idx_last_activated */
   COG_PF_MOVES = 2,  /* n_movements u32 */
   COG_PF_LOC = 3,    /* int16 x | int16 y << 16, in half-hex units (2x the reference's float) */
-  COG_PF_MPLAY = 4, COG_PF_MSPEC = 5, COG_PF_MREM = 6, /* P[p] mask heads as bit sets */
+  COG_PF_MPLAY = 4, COG_PF_MSPEC = 5 /* unused: play_special is derived from play */,
+  COG_PF_MREM = 6, /* P[p] mask heads as bit sets */
   COG_PF_MMS = 7     /* P[p].move (bits 0-6) | P[p].get_from_shop (bits 7-25) */
 };
 /* env scalars (line 8) */
@@ -64,8 +66,10 @@ enum {
   COG_ES_MISC = 2,       /* byte0 agent_selection, byte1 phase, byte2 n_in_market */
   COG_ES_RES0 = 3, COG_ES_RES1 = 4, COG_ES_RES2 = 5, /* current_resources * 2 (int32) */
   COG_ES_MIN = 6,        /* int16 min_x | int16 min_y << 16 (half-hex units) */
-  COG_ES_SPLAY = 7, COG_ES_SSPEC = 8, COG_ES_SREM = 9, COG_ES_SMS = 10, /* S (selected mask) */
-  COG_ES_INFOSTEPS = 11  /* Info.agent_infos[k].steps_taken, byte k */
+  COG_ES_SPLAY = 7, COG_ES_SSPEC = 8 /* unused */, COG_ES_SREM = 9, COG_ES_SMS = 10, /* S (selected mask) */
+  COG_ES_INFOSTEPS = 11, /* Info.agent_infos[k].steps_taken, one byte per player (rotated) */
+  COG_ES_CPF = 12, COG_ES_CPC = 13 /* live COG_PF_FLAGS / COG_PF_COUNTS of the current agent
+                                      (that player's words in line 7 are stale) */
 };
 
 #endif
