@@ -109,25 +109,45 @@ __device__ __forceinline__ int hex_end(u32 c) { return (int)((c >> 6) & 1); }
 
 /* ----------------------------------------------------------- warp helpers */
 __device__ __forceinline__ u32 bcast(u32 v, int src) { return __shfl_sync(COG_FULL, v, src); }
+/* inclusive prefix sum over the warp.  shfl.up reports in a predicate whether the source
+ * lane exists, so every round is SHFL + one predicated IADD (no lane compares) */
 __device__ __forceinline__ u32 warp_incl_scan(u32 v, int lane) {
+#ifdef COG_EMU
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
     u32 t = __shfl_up_sync(COG_FULL, v, d);
     if (lane >= d) v += t;
   }
+#else
+  (void)lane;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1)
+    asm volatile("{ .reg .u32 t; .reg .pred q;\n\t"
+                 "shfl.sync.up.b32 t|q, %0, %1, 0, 0xffffffff;\n\t"
+                 "@q add.u32 %0, %0, t; }"
+                 : "+r"(v) : "r"(d));
+#endif
   return v;
+}
+/* (a & m) | (w & ~m) as ONE LOP3 (the compiler emits two for the C expression) */
+__device__ __forceinline__ u32 bitsel(u32 a, u32 m, u32 w) {
+#ifdef COG_EMU
+  return (a & m) | (w & ~m);
+#else
+  u32 d;
+  asm("lop3.b32 %0, %1, %2, %3, 0xE2;" : "=r"(d) : "r"(a), "r"(m), "r"(w));
+  return d;
+#endif
 }
 /* byte p of a word.  Written with shifts and masks so that a literal p (almost always 0,
  * see "rotated player order" below) folds to one LOP3 / one IADD + one LOP3 */
 __device__ __forceinline__ u32 getb(u32 w, int p) { return (w >> (8 * p)) & 0xffu; }
 __device__ __forceinline__ u32 setb(u32 w, int p, u32 v) {
-  const u32 m = 0xffu << (8 * p);
-  return (w & ~m) | ((v << (8 * p)) & m);
+  return bitsel(v << (8 * p), 0xffu << (8 * p), w);
 }
 /* u8 arithmetic inside byte p (wraps like the reference's u_char counters) */
 __device__ __forceinline__ u32 addb(u32 w, int p, int d) {
-  const u32 m = 0xffu << (8 * p);
-  return (w & ~m) | ((w + ((u32)d << (8 * p))) & m);
+  return bitsel(w + ((u32)d << (8 * p)), 0xffu << (8 * p), w);
 }
 /* rotate the four bytes of w right by r positions: byte r moves to byte 0 */
 __device__ __forceinline__ u32 rotb(u32 w, u32 r) { return __funnelshift_r(w, w, 8u * r); }
@@ -159,7 +179,7 @@ __device__ __forceinline__ u32 minstd_next(u32 &s) {
  * and past come from a constant table indexed by the warp-uniform n, and r / scaling is
  * a multiply-high by magic = floor(2^36 / scaling) + 1 — an over-estimate by less than
  * r / 2^36 < 1/32, so at most one too large — followed by one exact correction. */
-struct ud_entry { u32 scaling, past, magic, pad; };
+struct alignas(16) ud_entry { u32 scaling, past, magic, pad; };
 namespace tab {
 constexpr ud_entry ud_make(u32 n) {
   if (n == 0) return ud_entry{0, 0, 0, 0};
@@ -174,12 +194,8 @@ __constant__ const ud_entry UD_TAB[33] = {
     COG_UD(18), COG_UD(19), COG_UD(20), COG_UD(21), COG_UD(22), COG_UD(23), COG_UD(24), COG_UD(25), COG_UD(26),
     COG_UD(27), COG_UD(28), COG_UD(29), COG_UD(30), COG_UD(31), COG_UD(32)};
 
-__device__ __forceinline__ u32 uniform_draw(u32 &s, u32 n) {
-  if (n == 1) { /* scaling = past = 2147483645: only g() == 2147483646 is rejected; result 0 */
-    while (COG_UNLIKELY(minstd_next(s) == 2147483646u)) {}
-    return 0;
-  }
-  if (n <= 32) {
+__device__ __forceinline__ u32 uniform_draw(u32 &s, u32 n) { /* n >= 1 */
+  if (COG_LIKELY(n <= 32)) { /* n == 1: scaling = past = 2147483645, the result is 0 */
     const ud_entry e = UD_TAB[n];
     u32 r;
     do {
@@ -202,6 +218,12 @@ __device__ __forceinline__ u32 uniform_draw(u32 &s, u32 n) {
 __device__ __forceinline__ u32 nth_set_bit(u32 v, u32 j) {
   for (u32 t = 0; t < j; ++t) v &= v - 1u;
   return (u32)__ffs((int)v) - 1u;
+}
+/* the same without a loop: lane l owns bit l and knows how many set bits lie below it */
+__device__ __forceinline__ u32 nth_set_bit_warp(u32 v, u32 j, int lane) {
+  const u32 below = v & ((1u << lane) - 1u);
+  const u32 me = __ballot_sync(COG_FULL, ((v >> lane) & 1u) && (u32)__popc(below) == j);
+  return (u32)__ffs((int)me) - 1u;
 }
 
 /* one +60 degree step in half-hex axial coordinates: (x, y) -> (-y, x + y)
@@ -437,14 +459,19 @@ __device__ __forceinline__ void deck_draw(Env &E, u32 &pc, int p, u32 n, int lan
     n_in_draw = (n_in_draw + __reduce_add_sync(COG_FULL, d)) & 0xffu;
   }
   if (n_in_draw < n) n = n_in_draw;
+  /* one prefix sum for the whole batch: drawing a copy of card c lowers the cumulative
+   * counts of the lanes from c upwards by one (the picked pile entry is >= 1) */
+  u32 incl = n ? warp_incl_scan(getb(E.draw, p), lane) : 0u;
   for (u32 i = 0; i < n; ++i) {
     const u32 target = uniform_draw(E.rng, n_in_draw);
-    const int cl = pile_pick(E.draw, p, target, lane);
-    if (cl) {
+    const u32 hit = __ballot_sync(COG_FULL, incl > target);
+    if (COG_LIKELY(hit)) { /* no hit: target beyond the pile (UB in the reference) */
+      const int cl = __ffs((int)hit) - 1;
       if (lane == cl) {
         E.draw = addb(E.draw, p, -1);
         E.hand = addb(E.hand, p, 1);
       }
+      if (lane >= cl) --incl;
       E.Splay |= 1u << cl;
     }
     n_in_draw = (n_in_draw - 1) & 0xffu;
@@ -1005,9 +1032,10 @@ __device__ __forceinline__ int env_reset(Env &E, const Params &prm, const Buffer
 /* Out-of-line copy for the step kernels: episode ends are rare, and keeping board
  * generation out of the step loop's instruction stream (and register allocation) matters
  * more than the call.  The caller passes a COPY of its env so that its own stays in registers. */
-__device__ COG_NOINLINE int env_reset_outlined(Env &E, const Params &prm, const Buffers &B, u64 i,
-                                               BoardScratch &sc, int lane) {
-  return env_reset(E, prm, B, i, sc, lane);
+__device__ COG_NOINLINE int env_reset_outlined(Env &E, const Params prm, const Buffers B, u64 i,
+                                               BoardScratch *sc, int lane) {
+  /* prm, B by value: a reference would force the caller's copies into local memory */
+  return env_reset(E, prm, B, i, *sc, lane);
 }
 
 /* -------------------------------------------------------------------- step */
@@ -1231,7 +1259,7 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop_in, const Pa
       }
       if (lane < 4 && won) atomicAdd(&B.stats[4 + lane], 1ull);
       Env T = E; /* auto-reset, the RNG stream continues */
-      env_reset_outlined(T, prm, B, i, sc, lane);
+      env_reset_outlined(T, prm, B, i, &sc, lane);
       E = T;
       touched = 0xfu;
     }
@@ -1252,6 +1280,20 @@ __device__ __forceinline__ u32 sample_head(u32 &rng, u32 valid) {
   const u32 j = uniform_draw(rng, (u32)__popc(valid));
   return nth_set_bit(valid, j);
 }
+/* The `play` head on the hot path: no branch on the number of legal indices (a head with
+ * one legal index goes through the table like any other: scaling = past = 2147483645 gives
+ * 0), the n-th set bit found by the lanes.  A rejected draw — or an empty head, whose table
+ * entry has past = 0 — falls back to the step-by-step version with the state untouched. */
+__device__ __forceinline__ u32 sample_head_warp(u32 &rng, u32 valid, int lane) {
+  const ud_entry e = UD_TAB[__popc(valid)];
+  u32 s1 = rng;
+  const u32 r = minstd_next(s1) - 1u;
+  if (COG_UNLIKELY(r >= e.past)) return sample_head(rng, valid);
+  rng = s1;
+  u32 q = __umulhi(r, e.magic) >> 4;
+  if (q * e.scaling > r) --q;
+  return nth_set_bit_warp(valid, q, lane);
+}
 /* Four consecutive draws over [0, 0] (heads whose only legal index is "none") advance
  * the engine four times and reject only an output of 2147483646 = -1 (mod m).  Output i
  * equals x a^i, so no rejection happens unless x = -a^-i for some i in 1..4; otherwise
@@ -1271,8 +1313,8 @@ __device__ __forceinline__ bool minstd_skip4_unit_draws(u32 &s) {
  * move | get_from_shop << 7): every producer builds them from lane-guarded ballots. */
 /* Returns true when only the `play` head had a choice (act < 256, a_shop = 0). */
 __device__ __forceinline__ bool sample_action(u32 &rng, u32 play, u32 spec, u32 rem, u32 ms, u32 &act,
-                                              u32 &a_shop) {
-  const u32 a0 = sample_head(rng, play);
+                                              u32 &a_shop, int lane) {
+  const u32 a0 = sample_head_warp(rng, play, lane);
   if (spec == 1u && rem == 1u && ms == 0x81u && minstd_skip4_unit_draws(rng)) {
     a_shop = 0; /* the reference's own flow: only `play` ever has a choice (SURVEY A#2) */
     act = a0;

@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, FUSED ? COG_MIN_BLOCKS : 6) k_s
       u32 act = 0, a_shop = 0, touched = 0;
       bool obs_pending = false;
       for (u32 k = 0; k < (u32)k_steps; ++k) {
-        if (sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop))
+        if (sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane))
           status = env_step<true, true>(E, act, 0, prm, B, i, sc, obs_pending, lane);
         else
           status = env_step<true, false>(E, act, a_shop, prm, B, i, sc, obs_pending, lane);
@@ -130,7 +130,7 @@ __global__ void k_sample(const u8 *__restrict__ masks, u32 *srng, u8 *actions, u
   const u32 move = __ballot_sync(COG_FULL, lane < 7 && m[COGL_AM_MOVE + lane]);
   const u32 shop = __ballot_sync(COG_FULL, lane < 19 && m[COGL_AM_SHOP + lane]);
   u32 sr = srng[i], act, a_shop;
-  sample_action(sr, play, spec, rem, move | (shop << 7), act, a_shop);
+  sample_action(sr, play, spec, rem, move | (shop << 7), act, a_shop, lane);
   __syncwarp(); /* every lane has read srng[i] before lane 0 overwrites it */
   if (lane == 0) srng[i] = sr;
   if (lane < 4) actions[i * COGL_ACTION_SIZE + lane] = (u8)(act >> (8 * lane));
