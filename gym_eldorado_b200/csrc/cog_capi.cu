@@ -154,6 +154,7 @@ int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device, void 
       {(void **)&h->B.agents, n},
       {(void **)&h->B.stats, COG_STAT_COUNT * sizeof(unsigned long long)},
       {(void **)&h->B.err, 2 * sizeof(int)},
+      {(void **)&h->B.park, 2 * sizeof(unsigned)},
   };
   for (auto &b : bufs) {
     cudaError_t e = cudaMalloc(b.p, b.bytes);
@@ -164,9 +165,9 @@ int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device, void 
     }
   }
 #ifndef COG_EMU
-  CK(cudaFuncSetAttribute(cog::k_step<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
+  CK(cudaFuncSetAttribute(cog::k_step_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
   int per_sm = 0;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step<true>, cog::BLOCK_THREADS, scratch_bytes()));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_fused, cog::BLOCK_THREADS, 0));
   h->fused_blocks_per_sm = per_sm > 0 ? per_sm : 1;
 #endif
   COG_LAUNCH(cog::k_init, blocks_for(n), cog::BLOCK_THREADS, 0, h->stream, h->B, n);
@@ -182,7 +183,7 @@ int cog_vec_destroy(cog_vec *h) {
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
   void *ptrs[] = {h->B.hidden, h->B.grid, h->B.obs, h->B.masks, h->B.rewards,
-                  h->B.dones,  h->B.infos, h->B.agents, h->B.stats, h->B.err, h->act_staging};
+                  h->B.dones,  h->B.infos, h->B.agents, h->B.stats, h->B.err, h->B.park, h->act_staging};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   if (h->ev0) cudaEventDestroy(h->ev0);
@@ -226,8 +227,8 @@ int cog_vec_step(cog_vec *h, const void *d_actions) {
   if (!h->seeded) return fail(COG_ERR_NOT_RESET, "step() before reset()");
   CK(cudaSetDevice(h->device));
   time_begin(h);
-  COG_LAUNCH(cog::k_step<false>, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B,
-             h->prm, h->n, (const uint8_t *)d_actions, (uint32_t *)nullptr, (uint8_t *)nullptr, (uint64_t)1);
+  COG_LAUNCH(cog::k_step_single, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B,
+             h->prm, h->n, (const uint8_t *)d_actions);
   time_end(h);
   g_launches++;
   CK(cudaGetLastError());
@@ -356,10 +357,15 @@ int cog_vec_run_fused(cog_vec *h, cog_sampler *s, uint64_t k_steps) {
   const unsigned resident = (unsigned)(h->sm_count * h->fused_blocks_per_sm);
   if (grid > resident) grid = resident;
   time_begin(h);
-  COG_LAUNCH(cog::k_step<true>, grid, cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm, h->n,
-             (const uint8_t *)nullptr, s->srng, s->actions, k_steps);
+  if (k_steps) {
+    COG_LAUNCH(cog::k_step_fused, grid, cog::BLOCK_THREADS, 0, h->stream, h->B, h->prm, h->n, s->srng,
+               s->actions, (uint32_t)k_steps);
+    /* the envs whose episode ended (exits at once when there are none) */
+    COG_LAUNCH(cog::k_step_tail, grid, cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm, h->n,
+               s->srng, s->actions);
+    g_launches += 2;
+  }
   time_end(h);
-  g_launches++;
   CK(cudaGetLastError());
   return COG_OK;
 }

@@ -77,14 +77,15 @@ __device__ const u32 LANE_CONST[32] = {
     COG_LC(16), COG_LC(17), COG_LC(18), COG_LC(19), COG_LC(20), COG_LC(21), COG_LC(22), COG_LC(23),
     COG_LC(24), COG_LC(25), COG_LC(26), COG_LC(27), COG_LC(28), COG_LC(29), COG_LC(30), COG_LC(31)};
 constexpr u32 COG_SPECIAL_MASK = tab::special_mask();
-__device__ const u8 SLOT_CARD_D[18] = COG_SHOP_SLOT_CARD_INIT;
+__constant__ const u8 SLOT_CARD_D[18] = COG_SHOP_SLOT_CARD_INIT;
 
 /* piece geometry in half-hex units (src/map.cpp:446-462), hex codes and piece
  * attributes (:464-695); encodings in tools/extract_tables.py */
 __device__ const xy8 COORDS_LARGE[37] = COG_COORDS_LARGE_INIT;
 __device__ const xy8 COORDS_SMALL[16] = COG_COORDS_SMALL_INIT;
 __device__ const xy8 COORDS_END[3] = COG_COORDS_END_INIT;
-__device__ const piece_meta PIECE_META[COG_N_PIECES_TOTAL] = COG_PIECE_META_INIT;
+/* __constant__: read with warp-uniform indices and feeding control flow (uniform loads) */
+__constant__ const piece_meta PIECE_META[COG_N_PIECES_TOTAL] = COG_PIECE_META_INIT;
 __device__ const u8 PIECE_HEX[COG_N_PIECES_TOTAL][COG_PIECE_MAX_HEXES] = COG_PIECE_HEX_INIT;
 /* connection points per (host size, new size): MapPiece::get_ref_connection_points
  * src/map.cpp:203-263.  kind 0 LARGE->LARGE, 1 LARGE->SMALL, 2 LARGE->TRIPLE, 3 SMALL->LARGE */
@@ -258,6 +259,7 @@ struct Buffers {
   u8 *agents;    /* [n] */
   unsigned long long *stats; /* [COG_STAT_COUNT] */
   int *err;      /* [0] first error code, [1] env index */
+  unsigned *park; /* [0] envs ever parked by k_step_fused, [1] envs k_step_tail picked up again */
 };
 
 /* ROTATED PLAYER ORDER.  The seven words that hold one byte per player (the five piles,
@@ -301,23 +303,46 @@ __device__ __forceinline__ void env_rotate(Env &E, u32 r) {
   E.nbr = rotb(E.nbr, r);
   E.info_steps = rotb(E.info_steps, r);
 }
+/* Re-broadcast the warp-uniform fields from lane 0.  The values do not change; what changes
+ * is that ptxas can PROVE them uniform again (a shuffle from a fixed lane), which it cannot
+ * for values that came back through memory from an out-of-line call.  With uniform loop
+ * state the step loop needs no BSSY/BSYNC pairs and no BRA.DIV guards before its shuffles. */
+__device__ __forceinline__ void env_uniform(Env &E) {
+  E.rng = bcast(E.rng, 0); E.turn = bcast(E.turn, 0); E.agent = bcast(E.agent, 0);
+  E.phase = bcast(E.phase, 0); E.n_in_market = bcast(E.n_in_market, 0);
+  E.cpf = bcast(E.cpf, 0); E.cpc = bcast(E.cpc, 0); E.info_steps = bcast(E.info_steps, 0);
+  E.Splay = bcast(E.Splay, 0); E.Srem = bcast(E.Srem, 0); E.Sms = bcast(E.Sms, 0);
+  E.res[0] = (int)bcast((u32)E.res[0], 0); E.res[1] = (int)bcast((u32)E.res[1], 0);
+  E.res[2] = (int)bcast((u32)E.res[2], 0);
+  E.minx = (int)bcast((u32)E.minx, 0); E.miny = (int)bcast((u32)E.miny, 0);
+}
 __device__ __forceinline__ int loc_x(u32 w) { return (int)(int16_t)(w & 0xffffu); }
 __device__ __forceinline__ int loc_y(u32 w) { return (int)(int16_t)(w >> 16); }
 __device__ __forceinline__ u32 loc_pack(int x, int y) {
   return ((u32)x & 0xffffu) | ((u32)y << 16);
 }
 
-__device__ __forceinline__ void env_load(Env &E, const u32 *__restrict__ rec, int lane) {
+/* L2 = true: read through L2 (ld.global.cg).  For a record the SAME launch wrote earlier —
+ * lines that other lanes stored may still sit, stale, in this SM's L1. */
+template <bool L2 = false>
+__device__ __forceinline__ u32 hid_word(const u32 *rec, int w) {
+#ifndef COG_EMU
+  if (L2) return __ldcg(rec + w);
+#endif
+  return rec[w];
+}
+template <bool L2 = false>
+__device__ __forceinline__ void env_load(Env &E, const u32 *rec, int lane) {
   E.lc = LANE_CONST[lane];
-  E.draw = rec[COG_HL_DRAW * 32 + lane];
-  E.hand = rec[COG_HL_HAND * 32 + lane];
-  E.active = rec[COG_HL_ACTIVE * 32 + lane];
-  E.played = rec[COG_HL_PLAYED * 32 + lane];
-  E.discard = rec[COG_HL_DISCARD * 32 + lane];
-  E.shop = rec[COG_HL_SHOP * 32 + lane];
-  E.nbr = rec[COG_HL_NBR * 32 + lane];
-  const u32 pw = rec[COG_HL_PLAYER * 32 + lane];
-  const u32 ew = rec[COG_HL_ENV * 32 + lane];
+  E.draw = hid_word<L2>(rec, COG_HL_DRAW * 32 + lane);
+  E.hand = hid_word<L2>(rec, COG_HL_HAND * 32 + lane);
+  E.active = hid_word<L2>(rec, COG_HL_ACTIVE * 32 + lane);
+  E.played = hid_word<L2>(rec, COG_HL_PLAYED * 32 + lane);
+  E.discard = hid_word<L2>(rec, COG_HL_DISCARD * 32 + lane);
+  E.shop = hid_word<L2>(rec, COG_HL_SHOP * 32 + lane);
+  E.nbr = hid_word<L2>(rec, COG_HL_NBR * 32 + lane);
+  const u32 pw = hid_word<L2>(rec, COG_HL_PLAYER * 32 + lane);
+  const u32 ew = hid_word<L2>(rec, COG_HL_ENV * 32 + lane);
   const int q = lane & 3;
   E.pf = bcast(pw, 4 * COG_PF_FLAGS + q);
   E.pc = bcast(pw, 4 * COG_PF_COUNTS + q);
@@ -346,7 +371,7 @@ __device__ __forceinline__ void env_load(Env &E, const u32 *__restrict__ rec, in
   E.cpc = bcast(ew, COG_ES_CPC);
 }
 
-__device__ __forceinline__ void env_store(const Env &E, u32 *__restrict__ rec, int lane) {
+__device__ __forceinline__ void env_store(const Env &E, u32 *rec, int lane, u32 pending = 0) {
   rec[COG_HL_DRAW * 32 + lane] = E.draw;
   rec[COG_HL_HAND * 32 + lane] = E.hand;
   rec[COG_HL_ACTIVE * 32 + lane] = E.active;
@@ -380,6 +405,7 @@ __device__ __forceinline__ void env_store(const Env &E, u32 *__restrict__ rec, i
   case COG_ES_INFOSTEPS: ew = E.info_steps; break;
   case COG_ES_CPF: ew = E.cpf; break;
   case COG_ES_CPC: ew = E.cpc; break;
+  case COG_ES_PENDING: ew = pending; break;
   default: break;
   }
   rec[COG_HL_ENV * 32 + lane] = ew;
@@ -713,7 +739,9 @@ __device__ __forceinline__ int bg_add_piece(BoardScratch &sc, BoardState &st, in
                                             int rotation, int lane) {
   const int r = rotation % 6;
   if (st.n_list >= BG_MAX_PLACED) return -3;
-  const int rot = sc.pose[piece].rot + r, cx = sc.pose[piece].cx + px, cy = sc.pose[piece].cy + py;
+  /* (shared-memory reads that steer control flow go through a broadcast: provably uniform) */
+  const int rot = (int)bcast((u32)(sc.pose[piece].rot + r), 0), cx = (int)bcast((u32)(sc.pose[piece].cx + px), 0),
+            cy = (int)bcast((u32)(sc.pose[piece].cy + py), 0);
   __syncwarp();
   if (lane == 0) {
     sc.pose[piece].rot = (int16_t)rot;
@@ -796,7 +824,7 @@ __device__ __forceinline__ int bg_add_random_piece(BoardScratch &sc, BoardState 
   u32 my_valid = 0; /* lane k keeps the valid-entry bit set of host k */
   int n_valid = 0;
   for (int k = 0; k < st.n_list; ++k) {
-    const int host = sc.placed[k].piece;
+    const int host = (int)bcast((u32)sc.placed[k].piece, 0);
     int kind, n_alt = 1, first_opt = 0, n_opts = 0;
     const int n_ent = bg_conn_kind(host, piece, kind, n_alt, first_opt, n_opts);
     bool ok = false;
@@ -825,11 +853,14 @@ __device__ __forceinline__ int bg_add_random_piece(BoardScratch &sc, BoardState 
   const u32 vm = bcast(my_valid, k);
   const u32 within = idx - (bcast(incl, k) - bcast(cnt, k));
   const int e = (int)nth_set_bit(vm, within);
-  const int host = sc.placed[k].piece;
+  const int host = (int)bcast((u32)sc.placed[k].piece, 0);
   int kind, n_alt = 1, first_opt = 0, n_opts = 1;
   bg_conn_kind(host, piece, kind, n_alt, first_opt, n_opts);
   int x, y, rot_add;
   bg_conn_entry(sc, host, kind, n_alt, e, x, y, rot_add);
+  x = (int)bcast((u32)x, 0);
+  y = (int)bcast((u32)y, 0);
+  rot_add = (int)bcast((u32)rot_add, 0);
   const int rot_idx = (int)uniform_draw(rng, (u32)n_opts);
   const int rc = bg_add_piece(sc, st, piece, x, y, bg_rot_option(kind, rot_idx) + rot_add, lane);
   return rc ? rc : 1;
@@ -841,58 +872,56 @@ __device__ __forceinline__ int bg_add_random_piece(BoardScratch &sc, BoardState 
 __device__ __forceinline__ int bg_generate(BoardScratch &sc, BoardState &st, u32 rng0, int n_pieces,
                                            int difficulty, int lane) {
   enum { F_ENTER = 0, F_LOOP = 1, F_DONE = 2, MAX_DEPTH = 5 };
-  u32 f_rng[MAX_DEPTH];
-  u64 f_valid[MAX_DEPTH]; /* valid_indices as a list of nibbles */
-  int f_nvalid[MAX_DEPTH], f_i[MAX_DEPTH], f_state[MAX_DEPTH];
-  int depth = 0;
-  f_rng[0] = rng0;
-  f_state[0] = F_ENTER;
+  /* the running frame lives in registers; parents wait on a small stack.  Popped values go
+   * through a broadcast so that they stay provably warp-uniform (see env_uniform) */
+  u32 s_rng[MAX_DEPTH];
+  u64 s_valid[MAX_DEPTH];
+  int s_nvalid[MAX_DEPTH], s_i[MAX_DEPTH], s_state[MAX_DEPTH];
+  u32 rng = rng0;
+  u64 valid = 0; /* valid_indices as a list of nibbles */
+  int nvalid = 0, fi = 0, state = F_ENTER, depth = 0;
   if (lane < 2) { /* the start pieces are never moved */
     sc.pose[lane].cx = 0; sc.pose[lane].cy = 0; sc.pose[lane].rot = 0;
   }
   __syncwarp();
   for (;;) {
-    if (f_state[depth] == F_ENTER) {
-      const int start = (int)uniform_draw(f_rng[depth], 2);
+    if (state == F_ENTER) {
+      const int start = (int)uniform_draw(rng, 2);
       const int rc = bg_add_piece(sc, st, start, 0, 0, 0, lane);
       if (rc) return rc;
-      u64 v = 0;
-      int nv = 0;
+      valid = 0;
+      nvalid = 0;
       for (int i = 0; i < 16; ++i)
-        if ((int)PIECE_META[2 + i].difficulty <= difficulty) v |= (u64)i << (4 * nv++);
-      f_valid[depth] = v;
-      f_nvalid[depth] = nv;
-      f_i[depth] = 0;
-      f_state[depth] = F_LOOP;
-    } else if (f_state[depth] == F_LOOP) {
+        if ((int)PIECE_META[2 + i].difficulty <= difficulty) valid |= (u64)i << (4 * nvalid++);
+      fi = 0;
+      state = F_LOOP;
+    } else if (state == F_LOOP) {
       bool descend = false;
-      if (f_i[depth] < n_pieces) {
+      if (fi < n_pieces) {
         int success = 0, next_idx = 0;
-        if (f_nvalid[depth]) {
-          const u32 pos = uniform_draw(f_rng[depth], (u32)f_nvalid[depth]);
-          next_idx = (int)((f_valid[depth] >> (4 * pos)) & 15u);
-          success = bg_add_random_piece(sc, st, 2 + next_idx, f_rng[depth], lane);
+        if (nvalid) {
+          const u32 pos = uniform_draw(rng, (u32)nvalid);
+          next_idx = (int)((valid >> (4 * pos)) & 15u);
+          success = bg_add_random_piece(sc, st, 2 + next_idx, rng, lane);
           if (success < 0) return success;
         }
-        f_i[depth]++;
+        fi++;
         if (success) {
           /* valid_indices.erase(begin + next_idx): the piece index is used as a POSITION;
            * past-the-end degenerates to pop_back (libstdc++ bits/vector.tcc:182-190) */
-          const int nv = f_nvalid[depth];
-          if (next_idx < nv - 1) {
-            const u64 v = f_valid[depth];
-            const u64 low = v & ((1ull << (4 * next_idx)) - 1ull);
-            f_valid[depth] = low | ((v >> (4 * (next_idx + 1))) << (4 * next_idx));
+          if (next_idx < nvalid - 1) {
+            const u64 low = valid & ((1ull << (4 * next_idx)) - 1ull);
+            valid = low | ((valid >> (4 * (next_idx + 1))) << (4 * next_idx));
           }
-          f_nvalid[depth] = nv - 1;
+          nvalid--;
         } else {
           descend = true; /* generate(..., failures + 1, rng) WITHOUT reset, then carry on */
         }
       } else {
-        const int endp = 18 + (int)uniform_draw(f_rng[depth], 2);
-        const int ok = bg_add_random_piece(sc, st, endp, f_rng[depth], lane);
+        const int endp = 18 + (int)uniform_draw(rng, 2);
+        const int ok = bg_add_random_piece(sc, st, endp, rng, lane);
         if (ok < 0) return ok;
-        f_state[depth] = F_DONE;
+        state = F_DONE;
         if (!ok) {
           bg_map_reset(sc, st, lane);
           descend = true;
@@ -900,13 +929,22 @@ __device__ __forceinline__ int bg_generate(BoardScratch &sc, BoardState &st, u32
       }
       if (descend) {
         if (depth + 1 >= MAX_DEPTH) return -2; /* failures >= MAX_FAILURES throws */
-        f_rng[depth + 1] = f_rng[depth];
-        f_state[depth + 1] = F_ENTER;
+        s_rng[depth] = rng; /* the callee starts from a COPY of the caller's engine */
+        s_valid[depth] = valid;
+        s_nvalid[depth] = nvalid;
+        s_i[depth] = fi;
+        s_state[depth] = state;
+        state = F_ENTER;
         depth++;
       }
     } else {
       if (depth == 0) return 0;
       depth--;
+      rng = bcast(s_rng[depth], 0);
+      valid = (u64)bcast((u32)s_valid[depth], 0) | ((u64)bcast((u32)(s_valid[depth] >> 32), 0) << 32);
+      nvalid = (int)bcast((u32)s_nvalid[depth], 0);
+      fi = (int)bcast((u32)s_i[depth], 0);
+      state = (int)bcast((u32)s_state[depth], 0);
     }
   }
 }
@@ -1029,14 +1067,6 @@ __device__ __forceinline__ int env_reset(Env &E, const Params &prm, const Buffer
   if (lane == 0) atomicAdd(&B.stats[10 /* COG_STAT_RESETS */], 1ull);
   return 0;
 }
-/* Out-of-line copy for the step kernels: episode ends are rare, and keeping board
- * generation out of the step loop's instruction stream (and register allocation) matters
- * more than the call.  The caller passes a COPY of its env so that its own stays in registers. */
-__device__ COG_NOINLINE int env_reset_outlined(Env &E, const Params prm, const Buffers B, u64 i,
-                                               BoardScratch *sc, int lane) {
-  /* prm, B by value: a reference would force the caller's copies into local memory */
-  return env_reset(E, prm, B, i, *sc, lane);
-}
 
 /* -------------------------------------------------------------------- step */
 /* cog_env::next_agent src/environment.cpp:79-89 */
@@ -1059,10 +1089,55 @@ __device__ __forceinline__ void env_next_agent(Env &E, u32 pf, u32 &pc, int p, u
   E.turn++;
 }
 
+/* Episode end, src/environment.cpp:187-207 + get_reward :281-288: rewards, Info and the
+ * episode aggregates.  Leaves the env in absolute player order, ready for env_reset().
+ * Kept out of env_step so that the fused hot kernel carries no episode-end code at all. */
+__device__ __forceinline__ void env_finish_episode(Env &E, const Params &prm, const Buffers &B, u64 i, int lane) {
+  env_to_absolute(E, lane); /* absolute player order for the bookkeeping below */
+  const u32 np = prm.n_players < 4 ? prm.n_players : 4;
+  const bool won = lane < 4 && (E.pf & PFL_WON);
+  const u32 winners = __ballot_sync(COG_FULL, won); /* get_reward :281-288 sums all 4 slots */
+  const int n_winners = __popc(winners);
+  u8 *info = B.infos + i * COGL_INFO_SIZE;
+  if (lane == 0) *reinterpret_cast<u32 *>(info) = E.turn; /* total_length = turn_counter */
+  if (lane < (int)np) {
+    u8 *ai = info + COGL_INFO_AGENT + COGL_INFO_AGENT_STRIDE * lane;
+    const float ret = (float)((int)prm.n_players * (won ? 1 : 0) - n_winners);
+    const u32 added = getb(E.pf, 2);
+    ai[0] = (u8)getb(E.pf, 3);
+    *reinterpret_cast<float *>(ai + 4) = ret;
+    *reinterpret_cast<u32 *>(ai + 8) = E.pmv;
+    ai[12] = (u8)added;
+    ai[13] = (u8)added; /* get_n_removed returns n_added_cards src/player.cpp:224 */
+    *reinterpret_cast<u32 *>(ai + 16) = 0;
+    *reinterpret_cast<u32 *>(ai + 20) = 0;
+    *reinterpret_cast<u32 *>(ai + 24) = 0;
+    *reinterpret_cast<u32 *>(ai + 28) = added; /* get_n_discarded also returns it :223 */
+    B.rewards[i * 4 + lane] = ret;
+  }
+  /* info steps_taken bytes now mirror the players' counters */
+  u32 steps = E.info_steps;
+  for (u32 k = 0; k < np; ++k) steps = setb(steps, (int)k, getb(bcast(E.pf, (int)k), 3));
+  E.info_steps = steps;
+  /* episode aggregates (reduced across GPUs by the host) */
+  const u32 moved = __reduce_add_sync(COG_FULL, lane < (int)np ? E.pmv : 0u);
+  const u32 added = __reduce_add_sync(COG_FULL, lane < (int)np ? getb(E.pf, 2) : 0u);
+  if (lane == 0) {
+    atomicAdd(&B.stats[1], 1ull);
+    if (!n_winners) atomicAdd(&B.stats[2], 1ull);
+    atomicAdd(&B.stats[3], (unsigned long long)E.turn);
+    atomicAdd(&B.stats[8], (unsigned long long)moved);
+    atomicAdd(&B.stats[9], (unsigned long long)added);
+  }
+  if (lane < 4 && won) atomicAdd(&B.stats[4 + lane], 1ull);
+}
+
 /* cog_env::step src/environment.cpp:91-224 followed by vec_cog_env::step_single's
  * auto-reset (include/vec_environment.h:53-61).  `act` = the five ActionData bytes
  * packed play | special<<8 | remove<<16 | move<<24, shop separately.
- * Returns: bit0 done, bits 8-11 players whose exported records changed.
+ * Returns: bit0 done, bits 8-11 players whose exported records changed.  When done, the
+ * CALLER must run env_finish_episode() and env_reset() next (kept out of this function so
+ * that each kernel holds ONE inlined copy of them — and the fused hot kernel none).
  *
  * LAZY (the fused kernel): update_observation is a pure function of the state the step
  * leaves behind and its result (P[agent].move / .get_from_shop) is only ever read by a
@@ -1072,7 +1147,7 @@ __device__ __forceinline__ void env_next_agent(Env &E, u32 pf, u32 &pc, int p, u
  * the caller runs it once after its last step. */
 template <bool LAZY, bool PLAY_ONLY>
 __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop_in, const Params &prm, const Buffers &B,
-                                        u64 i, BoardScratch &sc, bool &obs_pending, int lane) {
+                                        u64 i, bool &obs_pending, int lane) {
   /* PLAY_ONLY: the caller knows that only the `play` head can be non-zero (the sampler's
    * fast path) — every other branch of the step folds away at compile time */
   const u32 a_play = act & 0xffu;
@@ -1221,47 +1296,7 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop_in, const Pa
     if (COG_UNLIKELY(finished)) {
       done = 1;
       obs_pending = false;
-      env_to_absolute(E, lane); /* absolute player order for the bookkeeping below */
-      const u32 np = prm.n_players < 4 ? prm.n_players : 4;
-      const bool won = lane < 4 && (E.pf & PFL_WON);
-      const u32 winners = __ballot_sync(COG_FULL, won); /* get_reward :281-288 sums all 4 slots */
-      const int n_winners = __popc(winners);
-      u8 *info = B.infos + i * COGL_INFO_SIZE;
-      if (lane == 0) *reinterpret_cast<u32 *>(info) = E.turn; /* total_length = turn_counter */
-      if (lane < (int)np) {
-        u8 *ai = info + COGL_INFO_AGENT + COGL_INFO_AGENT_STRIDE * lane;
-        const float ret = (float)((int)prm.n_players * (won ? 1 : 0) - n_winners);
-        const u32 added = getb(E.pf, 2);
-        ai[0] = (u8)getb(E.pf, 3);
-        *reinterpret_cast<float *>(ai + 4) = ret;
-        *reinterpret_cast<u32 *>(ai + 8) = E.pmv;
-        ai[12] = (u8)added;
-        ai[13] = (u8)added; /* get_n_removed returns n_added_cards src/player.cpp:224 */
-        *reinterpret_cast<u32 *>(ai + 16) = 0;
-        *reinterpret_cast<u32 *>(ai + 20) = 0;
-        *reinterpret_cast<u32 *>(ai + 24) = 0;
-        *reinterpret_cast<u32 *>(ai + 28) = added; /* get_n_discarded also returns it :223 */
-        B.rewards[i * 4 + lane] = ret;
-      }
-      /* info steps_taken bytes now mirror the players' counters */
-      u32 steps = E.info_steps;
-      for (u32 k = 0; k < np; ++k) steps = setb(steps, (int)k, getb(bcast(E.pf, (int)k), 3));
-      E.info_steps = steps;
-      /* episode aggregates (reduced across GPUs by the host) */
-      const u32 moved = __reduce_add_sync(COG_FULL, lane < (int)np ? E.pmv : 0u);
-      const u32 added = __reduce_add_sync(COG_FULL, lane < (int)np ? getb(E.pf, 2) : 0u);
-      if (lane == 0) {
-        atomicAdd(&B.stats[1], 1ull);
-        if (!n_winners) atomicAdd(&B.stats[2], 1ull);
-        atomicAdd(&B.stats[3], (unsigned long long)E.turn);
-        atomicAdd(&B.stats[8], (unsigned long long)moved);
-        atomicAdd(&B.stats[9], (unsigned long long)added);
-      }
-      if (lane < 4 && won) atomicAdd(&B.stats[4 + lane], 1ull);
-      Env T = E; /* auto-reset, the RNG stream continues */
-      env_reset_outlined(T, prm, B, i, &sc, lane);
-      E = T;
-      touched = 0xfu;
+      touched = 0xfu; /* the caller runs env_reset next (auto-reset, the RNG stream continues) */
     }
   }
   return done | (touched << 8);

@@ -2,8 +2,8 @@
  *
  *   k_init        state of a default-constructed vec_cog_env<N>
  *   k_reset       vec_cog_env<N>::reset(...)  — board generation, decks, shop, masks, map encode
- *   k_step<false> vec_cog_env<N>::step(actions)  — single step, matches the Python API
- *   k_step<true>  persistent fused K x {sample(selected masks); step} with no host round trip
+ *   k_step_single vec_cog_env<N>::step(actions)  — single step, matches the Python API
+ *   k_step_fused  persistent fused K x {sample(selected masks); step} with no host round trip
  *   k_sample      vec_action_sampler<N>::sample(masks) on an arbitrary mask array
  */
 #ifndef COG_KERNELS_CUH
@@ -60,60 +60,153 @@ __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed)
   export_dynamic(E, B, i, 0xfu, lane);
 }
 
-/* FUSED = false: one step per env from `actions` (ActionData[n], 64-byte records).
- * FUSED = true : persistent; each warp walks envs with a grid stride, keeps the env in
- *                registers for k_steps x {sample; step}, then writes it back once.
- *                `srng` is the sampler's RNG array, `actions` receives the last action. */
+/* vec_cog_env<N>::step(actions): one step per env from `actions` (ActionData[n], 64-byte
+ * records), auto-reset included; exports only the records the step touched. */
+__global__ void __launch_bounds__(BLOCK_THREADS, 6) k_step_single(Buffers B, Params prm, u64 n,
+                                                                  const u8 *__restrict__ actions_in) {
+  const int lane = threadIdx.x & 31;
+  const u64 i = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  if (i >= n) return;
+  Env E;
+  env_load(E, B.hidden + i * COG_HID_WORDS, lane);
+  const u8 *a = actions_in + i * COGL_ACTION_SIZE;
+  const u32 mine = lane < 5 ? (u32)a[lane] : 0u;
+  const u32 act = bcast(mine, 0) | (bcast(mine, 1) << 8) | (bcast(mine, 2) << 16) | (bcast(mine, 3) << 24);
+  bool obs_pending = false;
+  const u32 status = env_step<false, false>(E, act, bcast(mine, 4), prm, B, i, obs_pending, lane);
+  if (status & 1u) {
+    env_finish_episode(E, prm, B, i, lane);
+    env_reset(E, prm, B, i, warp_scratch(), lane);
+  }
+  env_store(E, B.hidden + i * COG_HID_WORDS, lane);
+  export_dynamic(E, B, i, status >> 8, lane);
+  if (lane == 0) {
+    B.dones[i] = (u8)(status & 1u);
+    if ((i & (WARPS_PER_BLOCK - 1)) == 0) { /* one atomic per block */
+      const u64 left = n - i;
+      atomicAdd(&B.stats[0], (unsigned long long)(left < WARPS_PER_BLOCK ? left : WARPS_PER_BLOCK));
+    }
+  }
+}
+
+/* the sampler's five action bytes of env i */
+__device__ __forceinline__ void store_action(u8 *actions_out, u64 i, u32 act, u32 a_shop, int lane) {
+  if (lane < 4) actions_out[i * COGL_ACTION_SIZE + lane] = (u8)(act >> (8 * lane));
+  if (lane == 4) actions_out[i * COGL_ACTION_SIZE + 4] = (u8)a_shop;
+}
+
+/* Persistent fused path: k_steps x {vec_sampler.sample(selected masks); vec_env.step} with
+ * no host round trip.  Each warp walks envs with a grid stride and keeps the env in
+ * registers for all its iterations.
+ *
+ * Two kernels per launch.  k_step_fused is the hot loop and contains no episode-end code:
+ * an env whose episode ends leaves the loop and parks the iterations it still owes in its
+ * hidden record (COG_ES_PENDING).  k_step_tail, enqueued right behind it, picks those envs
+ * up, does the episode-end bookkeeping (rewards, Info, aggregates), resets them (board
+ * generation) and runs the rest with the general loop; it exits at once when nothing was
+ * parked.  The hot kernel is small (about 3 000 instructions against 9 000 with board
+ * generation inlined) and its register allocation is not shaped by the cold paths. */
 #ifndef COG_MIN_BLOCKS
 #define COG_MIN_BLOCKS 8
 #endif
-template <bool FUSED>
-__global__ void __launch_bounds__(BLOCK_THREADS, FUSED ? COG_MIN_BLOCKS : 6) k_step(Buffers B, Params prm, u64 n, const u8 *__restrict__ actions_in, u32 *srng,
-                       u8 *actions_out, u64 k_steps) {
+__global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step_fused(Buffers B, Params prm, u64 n, u32 *srng,
+                                                                             u8 *actions_out, u32 k_steps) {
   const int lane = threadIdx.x & 31;
+#ifdef COG_UNIFORM_PROOF
+  /* EXPERIMENT, off by default.  With the warp index taken through a shuffle from a fixed
+   * lane ptxas can prove the env loop and all env scalars warp-uniform and drops every
+   * BSSY/BSYNC pair and BRA.DIV guard from the loop (+8 % on the B200).  But the code it
+   * then emits keeps the loop counters in uniform registers and miscounts them as soon as
+   * episodes end with several envs per warp (CUDA 12.9, sm_100a): envs parked with wrong
+   * counts, steps counted twice.  tests/test_gpu_parity.py::test_fused_equals_single_steps
+   * (12000 envs) catches it.  Not used until that is understood. */
+  const u64 warp0 = (u64)blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0);
+#else
+  const u64 warp0 = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+#endif
+  const u64 stride = (u64)gridDim.x * WARPS_PER_BLOCK;
+  u64 steps_done = 0;
+  u32 n_parked = 0;
+  for (u64 i = warp0; i < n; i += stride) {
+    Env E;
+    env_load(E, B.hidden + i * COG_HID_WORDS, lane);
+    u32 sr = srng[i];
+    u32 act = 0, a_shop = 0, status = 0;
+    bool obs_pending = false;
+    u32 k = k_steps;
+    do {
+      if (sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane))
+        status = env_step<true, true>(E, act, 0, prm, B, i, obs_pending, lane);
+      else
+        status = env_step<true, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
+      --k;
+    } while (k && !(status & 1u));
+    steps_done += k_steps - k;
+    const u32 parked = (status & 1u) ? k + 1u : 0u;
+    if (obs_pending) env_update_observation(E, (int)E.agent, 0, E.cpc, lane);
+    __syncwarp(); /* every lane has read srng[i] before lane 0 overwrites it */
+    if (lane == 0) srng[i] = sr;
+    store_action(actions_out, i, act, a_shop, lane);
+    env_store(E, B.hidden + i * COG_HID_WORDS, lane, parked);
+    if (parked) {
+      ++n_parked;
+    } else {
+      export_dynamic(E, B, i, 0xfu, lane);
+      if (lane == 0) B.dones[i] = 0;
+    }
+  }
+  if (lane == 0) {
+    if (steps_done) atomicAdd(&B.stats[0], (unsigned long long)steps_done);
+    if (n_parked) atomicAdd(&B.park[0], n_parked);
+  }
+}
+
+/* second kernel of a fused launch: the envs whose episode ended in k_step_fused.
+ * park[0] counts envs ever parked, park[1] envs ever picked up again. */
+__global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step_tail(Buffers B, Params prm, u64 n, u32 *srng, u8 *actions_out) {
+  const int lane = threadIdx.x & 31;
+  if (*(volatile unsigned *)&B.park[0] == *(volatile unsigned *)&B.park[1]) return; /* nothing parked */
   const u64 warp0 = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
   const u64 stride = (u64)gridDim.x * WARPS_PER_BLOCK;
   BoardScratch &sc = warp_scratch();
   u64 steps_done = 0;
+  u32 n_handled = 0;
   for (u64 i = warp0; i < n; i += stride) {
+    const u32 parked = B.hidden[i * COG_HID_WORDS + COG_HL_ENV * 32 + COG_ES_PENDING];
+    if (!parked) continue;
+    ++n_handled;
     Env E;
     env_load(E, B.hidden + i * COG_HID_WORDS, lane);
-    u32 status = 0;
-    if (FUSED) {
-      u32 sr = srng[i];
-      u32 act = 0, a_shop = 0, touched = 0;
-      bool obs_pending = false;
-      for (u32 k = 0; k < (u32)k_steps; ++k) {
-        if (sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane))
-          status = env_step<true, true>(E, act, 0, prm, B, i, sc, obs_pending, lane);
-        else
-          status = env_step<true, false>(E, act, a_shop, prm, B, i, sc, obs_pending, lane);
-        touched |= status >> 8;
+    u32 sr = srng[i];
+    u32 act = 0, a_shop = 0, status = 1;
+    bool obs_pending = false;
+    const u32 k = parked - 1u;
+    for (u32 j = 0;; ++j) {
+      if (status & 1u) { /* rewards / Info / aggregates, then auto-reset: the RNG stream continues */
+        env_finish_episode(E, prm, B, i, lane);
+        env_reset(E, prm, B, i, sc, lane);
       }
-      if (obs_pending) env_update_observation(E, (int)E.agent, 0, E.cpc, lane);
-      __syncwarp(); /* every lane has read srng[i] before lane 0 overwrites it */
-      if (lane == 0) srng[i] = sr;
-      if (k_steps) {
-        if (lane < 4) actions_out[i * COGL_ACTION_SIZE + lane] = (u8)(act >> (8 * lane));
-        if (lane == 4) actions_out[i * COGL_ACTION_SIZE + 4] = (u8)a_shop;
-      }
-      status = (status & 1u) | (touched << 8);
-      steps_done += k_steps;
-    } else {
-      const u8 *a = actions_in + i * COGL_ACTION_SIZE;
-      const u32 mine = lane < 5 ? (u32)a[lane] : 0u;
-      const u32 act = bcast(mine, 0) | (bcast(mine, 1) << 8) | (bcast(mine, 2) << 16) | (bcast(mine, 3) << 24);
-      bool obs_pending = false;
-      status = env_step<false, false>(E, act, bcast(mine, 4), prm, B, i, sc, obs_pending, lane);
-      steps_done += 1;
+      if (j == k) break;
+      if (sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane))
+        status = env_step<true, true>(E, act, 0, prm, B, i, obs_pending, lane);
+      else
+        status = env_step<true, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
     }
+    steps_done += k;
+    if (obs_pending) env_update_observation(E, (int)E.agent, 0, E.cpc, lane);
+    __syncwarp();
+    if (lane == 0) srng[i] = sr;
+    if (k) store_action(actions_out, i, act, a_shop, lane);
     env_store(E, B.hidden + i * COG_HID_WORDS, lane);
-    if (!FUSED || k_steps) {
-      export_dynamic(E, B, i, status >> 8, lane);
-      if (lane == 0) B.dones[i] = (u8)(status & 1u);
-    }
+    export_dynamic(E, B, i, 0xfu, lane);
+    if (lane == 0) B.dones[i] = (u8)(status & 1u);
   }
-  if (lane == 0 && steps_done) atomicAdd(&B.stats[0], (unsigned long long)steps_done);
+  /* park[1] can only reach park[0] once EVERY parked env was picked up, so a warp that
+   * starts late never sees the counters equal while it still has work */
+  if (lane == 0) {
+    if (steps_done) atomicAdd(&B.stats[0], (unsigned long long)steps_done);
+    if (n_handled) atomicAdd(&B.park[1], n_handled);
+  }
 }
 
 /* vec_action_sampler<N>::sample include/vec_sampler.h:14-21 on ActionMask[n] records:

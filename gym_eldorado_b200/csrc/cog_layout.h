@@ -68,8 +68,11 @@ enum {
   COG_ES_MIN = 6,        /* int16 min_x | int16 min_y << 16 (half-hex units) */
   COG_ES_SPLAY = 7, COG_ES_SSPEC = 8 /* unused */, COG_ES_SREM = 9, COG_ES_SMS = 10, /* S (selected mask) */
   COG_ES_INFOSTEPS = 11, /* Info.agent_infos[k].steps_taken, one byte per player (rotated) */
-  COG_ES_CPF = 12, COG_ES_CPC = 13 /* live COG_PF_FLAGS / COG_PF_COUNTS of the current agent
-                                      (that player's words in line 7 are stale) */
+  COG_ES_CPF = 12, COG_ES_CPC = 13, /* live COG_PF_FLAGS / COG_PF_COUNTS of the current agent
+                                       (that player's words in line 7 are stale) */
+  COG_ES_PENDING = 14 /* only non-zero INSIDE a fused launch: 1 + the sample+step iterations this env
+                         still owes after an episode end (phase 2 of k_step<true> resets the env,
+                         runs them and clears the word) */
 };
 
 #endif

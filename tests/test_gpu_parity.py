@@ -70,7 +70,10 @@ def test_map_failure_is_reported(cuda_lib):
     c.close()
 
 
-@pytest.mark.parametrize("n,difficulty,max_steps,k", [(512, layout.MEDIUM, 100000, 300), (512, layout.HARD, 8, 300)])
+@pytest.mark.parametrize("n,difficulty,max_steps,k", [(512, layout.MEDIUM, 100000, 300), (512, layout.HARD, 8, 300),
+                                                      # more envs than resident warps: several envs per warp,
+                                                      # episode ends parked for the tail kernel
+                                                      (12000, layout.HARD, 8, 120), (12000, layout.EASY, 100000, 120)])
 def test_fused_equals_single_steps(cuda_lib, oracle_cls, n, difficulty, max_steps, k):
     """The persistent fused kernel == k x (sample(selected masks); step), bit for bit,
     and both == the oracle."""
