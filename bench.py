@@ -23,14 +23,26 @@ sys.path.insert(0, ROOT)
 # payload bytes that must move per sample+step when every exported buffer is
 # kept current each step (391 read + 305 written)
 ALGO_BYTES_PER_ENV_STEP = 696
+ALGO_BYTES_PER_RESET = 19440
 FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md
 
-WORKLOAD = {
-    "workload": "BASELINE configs[2]: 65,536 envs per GPU, 4 players, 3 pieces, MEDIUM, "
-                "max_steps 100000, masked random sampler, persistent fused step+sample kernel",
-    "n_envs_per_gpu": 65536, "n_players": 4, "n_pieces": 3, "difficulty": "MEDIUM",
-    "max_steps": 100000, "seed": 12345,
+# BASELINE.json configs (0-based index); [2] is the headline single-GPU workload
+WORKLOADS = {
+    2: {"workload": "BASELINE configs[2]: 65,536 envs per GPU, 4 players, 3 pieces, MEDIUM, "
+                    "max_steps 100000, masked random sampler, persistent fused step+sample kernel",
+        "n_envs_per_gpu": 65536, "n_players": 4, "n_pieces": 3, "difficulty": "MEDIUM",
+        "max_steps": 100000, "seed": 12345},
+    3: {"workload": "BASELINE configs[3] (reset-heavy): 65,536 envs per GPU, 2 players, 3 pieces, HARD, "
+                    "max_steps 8 turns, fused kernel with procedural board generation on every episode end",
+        "n_envs_per_gpu": 65536, "n_players": 2, "n_pieces": 3, "difficulty": "HARD",
+        "max_steps": 8, "seed": 12345},
+    4: {"workload": "BASELINE configs[4]: 1,048,576 envs sharded over the GPUs, 4 players, 3 pieces, HARD, "
+                    "max_steps 100000, fused kernel, NCCL-reduced episode statistics",
+        "n_envs_per_gpu": None, "n_envs_total": 1 << 20, "n_players": 4, "n_pieces": 3, "difficulty": "HARD",
+        "max_steps": 100000, "seed": 12345},
 }
+WORKLOAD = dict(WORKLOADS[2])
+DIFFICULTY = {"EASY": 0, "MEDIUM": 1, "HARD": 2}
 
 
 def parse():
@@ -39,11 +51,19 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--inner", type=int, default=256, help="fused sample+step iterations per launch")
-    ap.add_argument("--envs", type=int, default=WORKLOAD["n_envs_per_gpu"], help="envs per GPU")
+    ap.add_argument("--inner", type=int, default=1024, help="fused sample+step iterations per launch")
+    ap.add_argument("--config", type=int, default=2, choices=sorted(WORKLOADS), help="BASELINE.json configs index")
+    ap.add_argument("--envs", type=int, default=None, help="envs per GPU (default: the config's)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--no-resets", action="store_true")
+    args = ap.parse_args()
+    WORKLOAD.clear()
+    WORKLOAD.update(WORKLOADS[args.config])
+    if args.envs is None:
+        args.envs = WORKLOAD["n_envs_per_gpu"] or WORKLOAD["n_envs_total"] // max(1, args.gpus)
+    WORKLOAD["n_envs_per_gpu"] = args.envs
+    return args
 
 
 def peak_hbm():
@@ -105,16 +125,21 @@ def run_reference(args, bounded_seconds=None):
     if not refshim.available():
         kind = "port"
     n = args.envs
+    if refshim.available():  # the reference's templates are instantiated for these sizes only
+        n = max(k for k in refshim.SUPPORTED_N if k <= n)
     cores = os.cpu_count() or 1
     try:
         cores = len(os.sched_getaffinity(0))
     except Exception:
         pass
-    diff = 1
+    diff = DIFFICULTY[WORKLOAD["difficulty"]]
+    npl = WORKLOAD["n_players"]
+    if kind == "reference" and npl < 4:
+        npl = 4  # fewer than 4 players is undefined behaviour in the reference
     if kind == "reference":
         threads = max(1, min(cores - 1, 32))  # workers busy-wait and pin; never oversubscribe
         v = refshim.RefVec(n, WORKLOAD["seed"])
-        v.reset(WORKLOAD["seed"], 4, 3, diff, WORKLOAD["max_steps"])
+        v.reset(WORKLOAD["seed"], npl, 3, diff, WORKLOAD["max_steps"])
         v.runner(threads)
         mode = 1  # ThreadedRunner async (the reference's fastest mode)
         run = lambda k: v.time_run(k, mode)
@@ -123,7 +148,7 @@ def run_reference(args, bounded_seconds=None):
     else:
         from oracle import port
         v = port.OracleVec(n, WORKLOAD["seed"])
-        v.reset(WORKLOAD["seed"], 4, 3, diff, WORKLOAD["max_steps"])
+        v.reset(WORKLOAD["seed"], npl, 3, diff, WORKLOAD["max_steps"])
         run = v.time_run
         used = 1
         how = "oracle port (scalar C), 1 thread"
@@ -170,7 +195,7 @@ def main():
     import numpy as np
     import torch
     import torch.distributed as dist
-    from gym_eldorado_b200 import capi, layout
+    from gym_eldorado_b200 import capi, layout, shard
 
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
     torch.cuda.set_device(local_rank)
@@ -179,9 +204,12 @@ def main():
     L = capi.lib()
     n = args.envs
     offset = rank * n  # weak scaling: every GPU owns its own slice of global env indices
+    if WORKLOAD.get("n_envs_total") and args.envs * world == WORKLOAD["n_envs_total"]:
+        offset, stop = shard.shard_range(rank, world, WORKLOAD["n_envs_total"])  # config 4: fixed total
+        n = stop - offset
     vec = capi.VecHandle(n, offset, local_rank, None, L)
     smp = capi.SamplerHandle(n, WORKLOAD["seed"], offset, local_rank, None, L)
-    vec.reset(WORKLOAD["seed"], 4, 3, layout.MEDIUM, WORKLOAD["max_steps"])
+    vec.reset(WORKLOAD["seed"], WORKLOAD["n_players"], 3, DIFFICULTY[WORKLOAD["difficulty"]], WORKLOAD["max_steps"])
     launches0 = L.cog_kernel_launches()
     stats_t = torch.zeros(len(capi.STAT_NAMES), dtype=torch.int64, device="cuda")
 
@@ -208,10 +236,8 @@ def main():
         one_step()
         kernel_ms.append(None)
     # the one data-path-free collective: aggregate episode statistics over NVLink
-    st = vec.stats()
-    stats_t.copy_(torch.tensor([st[k] for k in capi.STAT_NAMES], dtype=torch.int64))
-    if world > 1:
-        dist.all_reduce(stats_t)
+    tot = shard.reduce_stats(vec.stats(), device="cuda")
+    stats_t.copy_(torch.tensor([tot[k] for k in capi.STAT_NAMES], dtype=torch.int64))
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
@@ -243,11 +269,37 @@ def main():
                 traffic = tj.get("dram_bytes_per_launch")
         except Exception:
             pass
-    roofline = {"bound": "hbm", "kernel": "cog::k_step<true> (fused sample+step)", "achieved": achieved,
+    roofline = {"bound": "hbm", "kernel": "cog::k_step_fused (+ k_step_tail for finished episodes)", "achieved": achieved,
                 "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": k_ms,
                 "note": "696 B per env-step (SURVEY 8d) x envs x inner; the fused kernel keeps env state in "
                         "registers, so real DRAM traffic is far lower and the kernel is issue-bound"}
+
+    # procedural board generation: full-batch resets (the reference's `time_reset` analogue)
+    resets = None
+    if not args.no_resets:
+        for _ in range(2):
+            vec.reset()
+        r_iters = 10
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        r0.record()
+        for _ in range(r_iters):
+            vec.reset()
+        r1.record()
+        barrier()
+        r_ms = r0.elapsed_time(r1) / r_iters
+        tr = torch.tensor([r_ms], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tr, op=dist.ReduceOp.MAX)
+        r_ms = float(tr.item())
+        resets = {"value": world * n / (r_ms * 1e-3), "unit": "resets/s", "ms_per_batch_reset": r_ms,
+                  "kernel": "cog::k_reset", "algorithmic_bytes_per_reset": ALGO_BYTES_PER_RESET,
+                  "achieved_GBs_per_gpu": ALGO_BYTES_PER_RESET * n / (r_ms * 1e-3) / 1e9,
+                  "frac_of_hbm_peak": ALGO_BYTES_PER_RESET * n / (r_ms * 1e-3) / 1e9 / peak,
+                  "note": "vec.reset() of all %d envs per GPU, %d timed launches (board generation is "
+                          "latency/issue bound, not HBM bound)" % (n, r_iters)}
+        # back to the benchmark trajectory state is not needed: e2e below starts from whatever state this leaves
 
     # end to end through the reference-facing call shape with HOST buffers: every step
     # copies that step's inputs (masks for sample(), actions for step()) from pinned host
@@ -307,9 +359,10 @@ def main():
                           (n * (17216 + 128 + 192 + 18 + 4 * 288 + 2304) / 1e9)})
         line = {"metric": "env-steps/sec (random masked policy)", "value": value, "unit": "env-steps/s",
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "higher_is_better": True, "scaling": "strong" if WORKLOAD.get("n_envs_total") else "weak",
+                "vs_baseline": None,
                 "dtype": "u8/u32 integer (f32 exports)", "data": "synthetic", "config": cfg,
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_timed,
+                "roofline": roofline, "resets": resets, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_timed,
                 "gpu_launches_total": launches, "clocks": clk,
                 "episode_stats": dict(zip(capi.STAT_NAMES, (int(x) for x in stats_t.tolist())))}
         print(json.dumps(line))

@@ -69,7 +69,7 @@ struct cog_vec {
   cog::Buffers B{};
   cog::Params prm{100000, 4, 3, 0}; /* cog_env::cog_env() defaults src/environment.cpp:10-15 */
   bool seeded = false;
-  int sm_count = 1, fused_blocks_per_sm = 1;
+  int sm_count = 1, fused_blocks_per_sm = 1, tail_blocks_per_sm = 1;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool timed = false;
   void *act_staging = nullptr; /* device copy of host actions for cog_vec_step_host */
@@ -169,6 +169,8 @@ int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device, void 
   int per_sm = 0;
   CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_fused, cog::BLOCK_THREADS, 0));
   h->fused_blocks_per_sm = per_sm > 0 ? per_sm : 1;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_tail, cog::BLOCK_THREADS, scratch_bytes()));
+  h->tail_blocks_per_sm = per_sm > 0 ? per_sm : 1;
 #endif
   COG_LAUNCH(cog::k_init, blocks_for(n), cog::BLOCK_THREADS, 0, h->stream, h->B, n);
   g_launches++;
@@ -360,8 +362,11 @@ int cog_vec_run_fused(cog_vec *h, cog_sampler *s, uint64_t k_steps) {
   if (k_steps) {
     COG_LAUNCH(cog::k_step_fused, grid, cog::BLOCK_THREADS, 0, h->stream, h->B, h->prm, h->n, s->srng,
                s->actions, (uint32_t)k_steps);
-    /* the envs whose episode ended (exits at once when there are none) */
-    COG_LAUNCH(cog::k_step_tail, grid, cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm, h->n,
+    /* the envs whose episode ended (exits at once when there are none); its own resident grid */
+    unsigned tail_grid = blocks_for(h->n);
+    const unsigned tail_resident = (unsigned)(h->sm_count * h->tail_blocks_per_sm);
+    if (tail_grid > tail_resident) tail_grid = tail_resident;
+    COG_LAUNCH(cog::k_step_tail, tail_grid, cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm, h->n,
                s->srng, s->actions);
     g_launches += 2;
   }

@@ -106,8 +106,11 @@ __device__ __forceinline__ void store_action(u8 *actions_out, u64 i, u32 act, u3
  * generation) and runs the rest with the general loop; it exits at once when nothing was
  * parked.  The hot kernel is small (about 3 000 instructions against 9 000 with board
  * generation inlined) and its register allocation is not shaped by the cold paths. */
+#ifndef COG_TAIL_BLOCKS
+#define COG_TAIL_BLOCKS 8 /* board generation is latency-bound: occupancy beats spills */
+#endif
 #ifndef COG_MIN_BLOCKS
-#define COG_MIN_BLOCKS 8
+#define COG_MIN_BLOCKS 9
 #endif
 __global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step_fused(Buffers B, Params prm, u64 n, u32 *srng,
                                                                              u8 *actions_out, u32 k_steps) {
@@ -163,7 +166,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step_fused(Bu
 
 /* second kernel of a fused launch: the envs whose episode ended in k_step_fused.
  * park[0] counts envs ever parked, park[1] envs ever picked up again. */
-__global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step_tail(Buffers B, Params prm, u64 n, u32 *srng, u8 *actions_out) {
+__global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Buffers B, Params prm, u64 n, u32 *srng, u8 *actions_out) {
   const int lane = threadIdx.x & 31;
   if (*(volatile unsigned *)&B.park[0] == *(volatile unsigned *)&B.park[1]) return; /* nothing parked */
   const u64 warp0 = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
