@@ -57,6 +57,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-resets", action="store_true")
+    ap.add_argument("--no-side", action="store_true", help="skip the regime-M / reset-heavy side measurements")
     args = ap.parse_args()
     WORKLOAD.clear()
     WORKLOAD.update(WORKLOADS[args.config])
@@ -301,6 +302,43 @@ def main():
                           "latency/issue bound, not HBM bound)" % (n, r_iters)}
         # back to the benchmark trajectory state is not needed: e2e below starts from whatever state this leaves
 
+    # the other single-GPU workloads SURVEY §8(d) asks for, as side measurements (same kernels,
+    # clearly labelled; the headline stays the config above): regime M = actions sampled from the
+    # merged legal mask (moves, purchases, wins: every branch of step live), and the reset-heavy
+    # configs[3] (HARD, 8 turns per episode, 2 players: board generation inside the step loop)
+    side = None
+    if not args.no_side:
+        side = {}
+        for name, diffc, npl, max_steps, merged in (("regime_M_merged_masks", WORKLOAD["difficulty"], 4, 100000, True),
+                                                    ("reset_heavy_configs3", "HARD", 2, 8, False)):
+            v2 = capi.VecHandle(n, offset, local_rank, None, L)
+            s2 = capi.SamplerHandle(n, WORKLOAD["seed"], offset, local_rank, None, L)
+            v2.reset(WORKLOAD["seed"], npl, 3, DIFFICULTY[diffc], max_steps)
+            inner2, reps = 256, 5
+            for _ in range(2):
+                v2.run_fused(s2, inner2, merged=merged)
+            v2.stats_reset()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            a0.record()
+            for _ in range(reps):
+                v2.run_fused(s2, inner2, merged=merged)
+            a1.record()
+            barrier()
+            tm = torch.tensor([a0.elapsed_time(a1)], dtype=torch.float64, device="cuda")
+            if world > 1:
+                dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            st2 = shard.reduce_stats(v2.stats(), device="cuda")
+            sec = float(tm.item()) * 1e-3
+            side[name] = {"value": st2["env_steps"] / sec, "unit": "env-steps/s", "resets_per_s": st2["resets"] / sec,
+                          "episodes": st2["episodes"], "wins": sum(st2["wins_seat%d" % k] for k in range(4)),
+                          "truncations": st2["truncations"], "travelled_hexes": st2["travelled_hexes"],
+                          "cards_added": st2["cards_added"],
+                          "config": "%d envs per GPU, %d players, %s, max_steps %d, %d launches x %d iterations, %s" % (
+                              n, npl, diffc, max_steps, reps, inner2,
+                              "merged legal masks" if merged else "selected_action_masks")}
+            v2.close(); s2.close()
+
     # end to end through the reference-facing call shape with HOST buffers: every step
     # copies that step's inputs (masks for sample(), actions for step()) from pinned host
     # memory and reads the step's results back
@@ -362,7 +400,7 @@ def main():
                 "higher_is_better": True, "scaling": "strong" if WORKLOAD.get("n_envs_total") else "weak",
                 "vs_baseline": None,
                 "dtype": "u8/u32 integer (f32 exports)", "data": "synthetic", "config": cfg,
-                "roofline": roofline, "resets": resets, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_timed,
+                "roofline": roofline, "resets": resets, "side_workloads": side, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_timed,
                 "gpu_launches_total": launches, "clocks": clk,
                 "episode_stats": dict(zip(capi.STAT_NAMES, (int(x) for x in stats_t.tolist())))}
         print(json.dumps(line))

@@ -42,6 +42,8 @@ SYMBOLS = {
     "cog_sampler_actions": (_int, [_vp, _P(_vp)]),
     "cog_sampler_read_actions": (_int, [_vp, _vp, _sz]),
     "cog_vec_run_fused": (_int, [_vp, _vp, _u64]),
+    "cog_vec_run_fused_ex": (_int, [_vp, _vp, _u64, _int]),
+    "cog_vec_merged_masks": (_int, [_vp, _vp]),
     "cog_vec_stats": (_int, [_vp, _P(_u64), _sz]),
     "cog_vec_stats_reset": (_int, [_vp]),
     "cog_sync": (_int, [_vp]),
@@ -140,8 +142,12 @@ class VecHandle:
         check(self.L, self.L.cog_vec_read(self._h, which, out.ctypes.data, out.nbytes))
         return out
 
-    def run_fused(self, sampler, k_steps):
-        check(self.L, self.L.cog_vec_run_fused(self._h, sampler._s, int(k_steps)))
+    def run_fused(self, sampler, k_steps, merged=False):
+        """k_steps x {sample; step} on the device; merged=True samples from the merged legal mask."""
+        check(self.L, self.L.cog_vec_run_fused_ex(self._h, sampler._s, int(k_steps), 1 if merged else 0))
+
+    def merged_masks_device(self, d_out_ptr):
+        check(self.L, self.L.cog_vec_merged_masks(self._h, d_out_ptr))
 
     def stats(self):
         out = (_u64 * len(STAT_NAMES))()

@@ -73,6 +73,7 @@ struct cog_vec {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool timed = false;
   void *act_staging = nullptr; /* device copy of host actions for cog_vec_step_host */
+  void *merged = nullptr;      /* COG_BUF_MERGED_MASKS, allocated on first use */
 };
 
 struct cog_sampler {
@@ -165,11 +166,12 @@ int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device, void 
     }
   }
 #ifndef COG_EMU
-  CK(cudaFuncSetAttribute(cog::k_step_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
+  CK(cudaFuncSetAttribute(cog::k_step_tail<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
   int per_sm = 0;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_fused, cog::BLOCK_THREADS, 0));
+  CK(cudaFuncSetAttribute(cog::k_step_tail<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_fused<false>, cog::BLOCK_THREADS, 0));
   h->fused_blocks_per_sm = per_sm > 0 ? per_sm : 1;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_tail, cog::BLOCK_THREADS, scratch_bytes()));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_tail<false>, cog::BLOCK_THREADS, scratch_bytes()));
   h->tail_blocks_per_sm = per_sm > 0 ? per_sm : 1;
 #endif
   COG_LAUNCH(cog::k_init, blocks_for(n), cog::BLOCK_THREADS, 0, h->stream, h->B, n);
@@ -185,7 +187,7 @@ int cog_vec_destroy(cog_vec *h) {
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
   void *ptrs[] = {h->B.hidden, h->B.grid, h->B.obs, h->B.masks, h->B.rewards,
-                  h->B.dones,  h->B.infos, h->B.agents, h->B.stats, h->B.err, h->B.park, h->act_staging};
+                  h->B.dones,  h->B.infos, h->B.agents, h->B.stats, h->B.err, h->B.park, h->act_staging, h->merged};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   if (h->ev0) cudaEventDestroy(h->ev0);
@@ -248,6 +250,13 @@ int cog_vec_buffer(cog_vec *h, int which, void **d_ptr, size_t *itemsize, size_t
   case COG_BUF_DONES: p = h->B.dones; item = 1; break;
   case COG_BUF_INFOS: p = h->B.infos; item = COG_INFO_SIZE; break;
   case COG_BUF_AGENT_SELECTION: p = h->B.agents; item = 1; break;
+  case COG_BUF_MERGED_MASKS:
+    if (!h->merged) {
+      CK(cudaSetDevice(h->device));
+      CK(cudaMalloc(&h->merged, h->n * COG_MASK_SIZE));
+      CK(cudaMemsetAsync(h->merged, 0, h->n * COG_MASK_SIZE, h->stream));
+    }
+    p = h->merged; item = COG_MASK_SIZE; break;
   default: return fail(COG_ERR_INVALID, "unknown buffer id");
   }
   if (d_ptr) *d_ptr = p;
@@ -348,7 +357,26 @@ int cog_vec_step_host(cog_vec *h, const void *h_actions) {
 }
 
 int cog_vec_run_fused(cog_vec *h, cog_sampler *s, uint64_t k_steps) {
+  return cog_vec_run_fused_ex(h, s, k_steps, COG_MASKS_SELECTED);
+}
+
+int cog_vec_merged_masks(cog_vec *h, void *d_out) {
+  if (!h) return fail(COG_ERR_INVALID, "NULL argument");
+  if (!h->seeded) return fail(COG_ERR_NOT_RESET, "merged masks before reset()");
+  CK(cudaSetDevice(h->device));
+  if (!d_out) {
+    int rc = cog_vec_buffer(h, COG_BUF_MERGED_MASKS, &d_out, nullptr, nullptr);
+    if (rc) return rc;
+  }
+  COG_LAUNCH(cog::k_merged_masks, blocks_for(h->n), cog::BLOCK_THREADS, 0, h->stream, h->B, h->n, (uint8_t *)d_out);
+  g_launches++;
+  CK(cudaGetLastError());
+  return COG_OK;
+}
+
+int cog_vec_run_fused_ex(cog_vec *h, cog_sampler *s, uint64_t k_steps, int mask_mode) {
   if (!h || !s) return fail(COG_ERR_INVALID, "NULL argument");
+  if (mask_mode != COG_MASKS_SELECTED && mask_mode != COG_MASKS_MERGED) return fail(COG_ERR_INVALID, "unknown mask mode");
   if (s->n != h->n || s->device != h->device) return fail(COG_ERR_INVALID, "sampler and envs differ in size or device");
   if (!h->seeded) return fail(COG_ERR_NOT_RESET, "run() before reset()");
   if (k_steps > 0xffffffffull) return fail(COG_ERR_INVALID, "k_steps must fit 32 bits");
@@ -360,14 +388,22 @@ int cog_vec_run_fused(cog_vec *h, cog_sampler *s, uint64_t k_steps) {
   if (grid > resident) grid = resident;
   time_begin(h);
   if (k_steps) {
-    COG_LAUNCH(cog::k_step_fused, grid, cog::BLOCK_THREADS, 0, h->stream, h->B, h->prm, h->n, s->srng,
-               s->actions, (uint32_t)k_steps);
+    if (mask_mode == COG_MASKS_MERGED)
+      COG_LAUNCH(cog::k_step_fused<true>, grid, cog::BLOCK_THREADS, 0, h->stream, h->B, h->prm, h->n, s->srng,
+                 s->actions, (uint32_t)k_steps);
+    else
+      COG_LAUNCH(cog::k_step_fused<false>, grid, cog::BLOCK_THREADS, 0, h->stream, h->B, h->prm, h->n, s->srng,
+                 s->actions, (uint32_t)k_steps);
     /* the envs whose episode ended (exits at once when there are none); its own resident grid */
     unsigned tail_grid = blocks_for(h->n);
     const unsigned tail_resident = (unsigned)(h->sm_count * h->tail_blocks_per_sm);
     if (tail_grid > tail_resident) tail_grid = tail_resident;
-    COG_LAUNCH(cog::k_step_tail, tail_grid, cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm, h->n,
-               s->srng, s->actions);
+    if (mask_mode == COG_MASKS_MERGED)
+      COG_LAUNCH(cog::k_step_tail<true>, tail_grid, cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm,
+                 h->n, s->srng, s->actions);
+    else
+      COG_LAUNCH(cog::k_step_tail<false>, tail_grid, cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm,
+                 h->n, s->srng, s->actions);
     g_launches += 2;
   }
   time_end(h);

@@ -1329,6 +1329,17 @@ __device__ __forceinline__ u32 sample_head_warp(u32 &rng, u32 valid, int lane) {
   if (q * e.scaling > r) --q;
   return nth_set_bit_warp(valid, q, lane);
 }
+/* The MERGED legal mask of the current agent: the reference splits
+ * the truth over two records — play / play_special live in S, move / get_from_shop / remove in
+ * P[agent] — and a remove bit only makes sense for a card still in hand.  Needs an
+ * up-to-date P[agent] (update_observation not deferred). */
+__device__ __forceinline__ void merged_heads(const Env &E, int lane, u32 &rem, u32 &ms) {
+  const int agent = (int)E.agent;
+  const u32 have = __ballot_sync(COG_FULL, lane >= 1 && lane <= 21 && getb(E.hand, 0) > 0);
+  rem = bcast(E.Prem, agent) & (have | 1u);
+  ms = bcast(E.Pms, agent);
+}
+
 /* Four consecutive draws over [0, 0] (heads whose only legal index is "none") advance
  * the engine four times and reject only an output of 2147483646 = -1 (mod m).  Output i
  * equals x a^i, so no rejection happens unless x = -a^-i for some i in 1..4; otherwise

@@ -112,6 +112,24 @@ __device__ __forceinline__ void store_action(u8 *actions_out, u64 i, u32 act, u3
 #ifndef COG_MIN_BLOCKS
 #define COG_MIN_BLOCKS 9
 #endif
+/* MERGED = false: actions sampled from selected_action_masks (the reference's own flow,
+ * "regime A": only `play` ever has a choice).  MERGED = true: from the merged legal mask of
+ * the current agent ("regime M": moves, purchases, removals, wins — every branch of step). */
+template <bool MERGED>
+__device__ __forceinline__ u32 sample_and_step(Env &E, u32 &sr, u32 &act, u32 &a_shop, const Params &prm,
+                                               const Buffers &B, u64 i, bool &obs_pending, int lane) {
+  if (MERGED) {
+    u32 rem, ms;
+    merged_heads(E, lane, rem, ms);
+    sample_action(sr, E.Splay, spec_of(E.Splay), rem, ms, act, a_shop, lane);
+    return env_step<false, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
+  }
+  if (sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane))
+    return env_step<true, true>(E, act, 0, prm, B, i, obs_pending, lane);
+  return env_step<true, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
+}
+
+template <bool MERGED>
 __global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step_fused(Buffers B, Params prm, u64 n, u32 *srng,
                                                                              u8 *actions_out, u32 k_steps) {
   const int lane = threadIdx.x & 31;
@@ -138,10 +156,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step_fused(Bu
     bool obs_pending = false;
     u32 k = k_steps;
     do {
-      if (sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane))
-        status = env_step<true, true>(E, act, 0, prm, B, i, obs_pending, lane);
-      else
-        status = env_step<true, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
+      status = sample_and_step<MERGED>(E, sr, act, a_shop, prm, B, i, obs_pending, lane);
       --k;
     } while (k && !(status & 1u));
     steps_done += k_steps - k;
@@ -166,6 +181,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step_fused(Bu
 
 /* second kernel of a fused launch: the envs whose episode ended in k_step_fused.
  * park[0] counts envs ever parked, park[1] envs ever picked up again. */
+template <bool MERGED>
 __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Buffers B, Params prm, u64 n, u32 *srng, u8 *actions_out) {
   const int lane = threadIdx.x & 31;
   if (*(volatile unsigned *)&B.park[0] == *(volatile unsigned *)&B.park[1]) return; /* nothing parked */
@@ -190,10 +206,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Bu
         env_reset(E, prm, B, i, sc, lane);
       }
       if (j == k) break;
-      if (sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane))
-        status = env_step<true, true>(E, act, 0, prm, B, i, obs_pending, lane);
-      else
-        status = env_step<true, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
+      status = sample_and_step<MERGED>(E, sr, act, a_shop, prm, B, i, obs_pending, lane);
     }
     steps_done += k;
     if (obs_pending) env_update_observation(E, (int)E.agent, 0, E.cpc, lane);
@@ -210,6 +223,18 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Bu
     if (steps_done) atomicAdd(&B.stats[0], (unsigned long long)steps_done);
     if (n_handled) atomicAdd(&B.park[1], n_handled);
   }
+}
+
+/* the merged legal mask of every env's current agent as ActionMask[n] records */
+__global__ void k_merged_masks(Buffers B, u64 n, u8 *out) {
+  const int lane = threadIdx.x & 31;
+  const u64 i = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  if (i >= n) return;
+  Env E;
+  env_load(E, B.hidden + i * COG_HID_WORDS, lane);
+  u32 rem, ms;
+  merged_heads(E, lane, rem, ms);
+  export_mask(out + i * COGL_MASK_SIZE, E.Splay, spec_of(E.Splay), rem, ms, lane);
 }
 
 /* vec_action_sampler<N>::sample include/vec_sampler.h:14-21 on ActionMask[n] records:

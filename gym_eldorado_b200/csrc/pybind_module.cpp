@@ -200,7 +200,8 @@ public:
     ck(cog_vec_buffer(own->h, which, &b.ptr, &b.itemsize, &b.count));
     switch (which) {
     case COG_BUF_OBS: b.np_dtype = layout_dtype("obs_dtype"); break;
-    case COG_BUF_SELECTED_MASKS: b.np_dtype = layout_dtype("action_mask_dtype"); break;
+    case COG_BUF_SELECTED_MASKS:
+    case COG_BUF_MERGED_MASKS: b.np_dtype = layout_dtype("action_mask_dtype"); break;
     case COG_BUF_INFOS: b.np_dtype = layout_dtype("info_dtype"); break;
     default: break;
     }
@@ -284,7 +285,9 @@ public:
   }
   void sync() { ck(cog_sync(env.own->h)); }
   void step_sync() { step(); sync(); }
-  void run(uint64_t k) { ck(cog_vec_run_fused(env.own->h, smp.own->s, k)); }
+  void run(uint64_t k, bool merged) {
+    ck(cog_vec_run_fused_ex(env.own->h, smp.own->s, k, merged ? COG_MASKS_MERGED : COG_MASKS_SELECTED));
+  }
 };
 
 /* get_vec_env(N) & co. return CLASS objects named like the reference's
@@ -351,6 +354,14 @@ PYBIND11_MODULE(COG_MODULE_NAME, m) {
       .def_property_readonly("infos", [](const VecEnv &e) { return e.view(COG_BUF_INFOS); })
       .def_property_readonly("agent_selection", [](const VecEnv &e) { return e.view(COG_BUF_AGENT_SELECTION); })
       .def_property_readonly("num_envs", [](const VecEnv &e) { return e.n; })
+      .def("merged_action_masks",
+           [](const VecEnv &e) {
+             ck(cog_vec_merged_masks(e.own->h, nullptr));
+             return e.view(COG_BUF_MERGED_MASKS);
+           },
+           "not in the reference: the merged legal mask of each env's current agent (play / play_special from "
+           "selected_action_masks; move / get_from_shop / remove from observations.player_data[agent].action_mask), "
+           "recomputed on every call into one persistent device buffer")
       .def("sync", [](VecEnv &e) { ck(cog_sync(e.own->h)); })
       .def("episode_stats", &VecEnv::stats)
       .def("reset_episode_stats", [](VecEnv &e) { ck(cog_vec_stats_reset(e.own->h)); });
@@ -368,8 +379,9 @@ PYBIND11_MODULE(COG_MODULE_NAME, m) {
       .def("step", &Runner::step)
       .def("step_sync", &Runner::step_sync)
       .def("sync", &Runner::sync)
-      .def("run", &Runner::run, py::arg("k_steps"),
-           "k_steps x {sample; step} in one persistent kernel, no host round trip")
+      .def("run", &Runner::run, py::arg("k_steps"), py::arg("merged_masks") = false,
+           "k_steps x {sample; step} on the device, no host round trip; merged_masks=True samples from the "
+           "merged legal mask of the current agent instead of selected_action_masks")
       .def("get_envs", [](Runner &r) { return r.env_obj; })
       .def("get_samplers", [](Runner &r) { return r.sampler_obj; })
       .def("get_actions", [](Runner &r) { return r.smp.get_actions(); })

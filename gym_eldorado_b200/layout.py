@@ -88,7 +88,7 @@ info_dtype = np.dtype({
 })
 
 # Which exported buffer is which (shared with include/cog_b200.h: enum cog_buffer)
-BUF_OBS, BUF_SELECTED_MASKS, BUF_REWARDS, BUF_DONES, BUF_INFOS, BUF_AGENT_SELECTION = range(6)
+BUF_OBS, BUF_SELECTED_MASKS, BUF_REWARDS, BUF_DONES, BUF_INFOS, BUF_AGENT_SELECTION, BUF_MERGED_MASKS = range(7)
 
 BUFFER_DTYPES = {
     BUF_OBS: obs_dtype,
@@ -97,6 +97,7 @@ BUFFER_DTYPES = {
     BUF_DONES: np.dtype(np.bool_),
     BUF_INFOS: info_dtype,
     BUF_AGENT_SELECTION: np.dtype(np.uint8),
+    BUF_MERGED_MASKS: action_mask_dtype,
 }
 
 

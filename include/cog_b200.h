@@ -60,7 +60,10 @@ typedef enum cog_buffer {
   COG_BUF_REWARDS = 2,         /* rewards                 float[n][4]        16 B */
   COG_BUF_DONES = 3,           /* dones                   bool[n]             1 B */
   COG_BUF_INFOS = 4,           /* infos                   Info[n]           192 B */
-  COG_BUF_AGENT_SELECTION = 5  /* agent_selection         uint8[n]            1 B */
+  COG_BUF_AGENT_SELECTION = 5, /* agent_selection         uint8[n]            1 B */
+  COG_BUF_MERGED_MASKS = 6     /* not in the reference: the merged legal mask of each env's current agent,
+                                  ActionMask[n]; allocated on first use, refreshed by
+                                  cog_vec_merged_masks(h, NULL) */
 } cog_buffer;
 
 /* episode aggregates accumulated on the device since cog_vec_create / the last
@@ -134,6 +137,22 @@ COG_API int cog_sampler_read_actions(cog_sampler *s, void *h_dst, size_t nbytes)
  * no host round trip; bit-identical to k_steps single sample+step calls.
  * The sampler's action buffer holds the last sampled actions afterwards. */
 COG_API int cog_vec_run_fused(cog_vec *h, cog_sampler *s, uint64_t k_steps);
+
+/* Which mask the fused loop samples from.  The reference keeps the legal actions of the
+ * current agent in TWO records: play / play_special in
+ * selected_action_masks, move / get_from_shop / remove in
+ * observations.player_data[agent].action_mask (include/api.h:104-131,
+ * src/environment.cpp:252-279).  COG_MASKS_SELECTED feeds the sampler
+ * selected_action_masks, exactly like the reference's README / pytest / asv loop (only `play`
+ * ever has a choice there).  COG_MASKS_MERGED feeds it the merged legal mask (play,
+ * play_special from S; move, get_from_shop from P[agent]; remove from P[agent] AND card
+ * still in hand): agents move, buy, remove and win. */
+enum { COG_MASKS_SELECTED = 0, COG_MASKS_MERGED = 1 };
+COG_API int cog_vec_run_fused_ex(cog_vec *h, cog_sampler *s, uint64_t k_steps, int mask_mode);
+/* the merged legal mask of every env's current agent, written as n_envs ActionMask records
+ * to DEVICE memory `d_out` (caller-owned, n_envs * COG_MASK_SIZE bytes), or, with d_out ==
+ * NULL, to the handle's own COG_BUF_MERGED_MASKS buffer */
+COG_API int cog_vec_merged_masks(cog_vec *h, void *d_out);
 
 /* episode aggregates (COG_STAT_COUNT uint64 values); synchronises the stream */
 COG_API int cog_vec_stats(cog_vec *h, uint64_t *out, size_t n);

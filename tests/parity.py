@@ -55,6 +55,20 @@ class Candidate:
             "actions": self.smp.read_actions(),
         }
 
+    def merged(self):
+        """cog_vec_merged_masks into a scratch buffer (device memory on the GPU box, host memory
+        under the emulator), returned as a host ActionMask array."""
+        nbytes = self.n * layout.action_mask_dtype.itemsize
+        if self.vec.L is _emu:
+            out = np.zeros(self.n, dtype=layout.action_mask_dtype)
+            self.vec.merged_masks_device(out.ctypes.data)
+            return out
+        import torch
+        t = torch.zeros(nbytes, dtype=torch.uint8, device="cuda")
+        self.vec.merged_masks_device(t.data_ptr())
+        self.vec.stats()  # synchronises the handle's stream
+        return t.cpu().numpy().view(layout.action_mask_dtype)
+
     def close(self):
         self.vec.close()
         self.smp.close()
@@ -149,3 +163,27 @@ def emu_module():
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     return mod
+
+
+def run_fused_merged_parity(library, oracle_cls, n, seed, difficulty, max_steps, chunks, n_players=4):
+    """Fused kernel sampling from the merged legal mask (regime M) against the oracle driven
+    step by step with host-merged masks; also checks cog_vec_merged_masks itself."""
+    o = oracle_cls(n, seed)
+    c = Candidate(library, n, seed)
+    try:
+        o.reset(seed, n_players, 3, difficulty, max_steps)
+        c.reset(seed, n_players, 3, difficulty, max_steps)
+        for k in chunks:
+            for _ in range(k):
+                o.sample(merged_masks(oracle_snapshot(o)))
+                o.step()
+            c.vec.run_fused(c.smp, k, merged=True)
+            snap = c.snapshot()
+            bad = first_mismatch(snap, oracle_snapshot(o))
+            assert bad is None, bad
+            want, got = merged_masks(snap), c.merged()
+            assert np.array_equal(pb(want), pb(got)), "cog_vec_merged_masks differs from the host merge"
+        return c.vec.stats()
+    finally:
+        c.close()
+        o.close()

@@ -46,3 +46,10 @@ def test_emulated_map_failure(emu):
 
 def test_emulated_offset_shard(emu, oracle_cls):
     parity.run_parity(emu, oracle_cls, 8, 31337, layout.MEDIUM, 50, 150, "M", offset=1000)
+
+
+def test_emulated_fused_merged_masks(emu, oracle_cls):
+    """regime M inside the fused kernel: moves, purchases, removals, wins, auto-resets"""
+    st = parity.run_fused_merged_parity(emu, oracle_cls, 12, 777, layout.EASY, 60, (1, 0, 37, 400))
+    assert st["episodes"] > 0 and st["travelled_hexes"] > 0 and st["cards_added"] > 0
+    assert st["env_steps"] == 12 * 438

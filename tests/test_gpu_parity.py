@@ -128,3 +128,15 @@ def test_full_size_properties(cuda_lib):
     assert (w["selected_action_masks"]["play"][:, 0]).all()    # index 0 always valid
     assert whole.vec.stats()["env_steps"] == n * k
     whole.close(); part.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,difficulty,max_steps,n_players", [(512, layout.EASY, 60, 4), (9000, layout.HARD, 40, 4),
+                                                             (256, layout.MEDIUM, 100000, 3)])
+def test_fused_merged_masks(cuda_lib, oracle_cls, n, difficulty, max_steps, n_players):
+    """The fused kernel sampling from the merged legal mask (moves, purchases, removals,
+    wins, auto-resets; several envs per warp) == the oracle, bit for bit."""
+    st = parity.run_fused_merged_parity(cuda_lib, oracle_cls, n, 31337, difficulty, max_steps, (1, 60, 300),
+                                        n_players=n_players)
+    assert st["episodes"] > 0 and st["travelled_hexes"] > 0
+    assert st["env_steps"] == n * 361

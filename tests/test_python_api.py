@@ -79,6 +79,21 @@ def _check_api(cog, oracle_cls, steps, n):
     r.sync()
     assert np.array_equal(pb(envs.observations.numpy()), pb(o.observations))
     assert envs.episode_stats()["env_steps"] == n * 45
+    # merged legal masks (not in the reference): a policy-in-the-loop step and the fused merged run
+    for _ in range(30):
+        m = envs.merged_action_masks()
+        assert np.array_equal(pb(m.numpy()), pb(parity.merged_masks({
+            "observations": envs.observations.numpy(), "agent_selection": envs.agent_selection.numpy(),
+            "selected_action_masks": envs.selected_action_masks.numpy()})))
+        smp.sample(m)                      # device buffer in, zero copy
+        envs.step(smp.get_actions())
+        o.sample(parity.merged_masks(parity.oracle_snapshot(o))); o.step()
+    r.run(40, merged_masks=True)
+    for _ in range(40):
+        o.sample(parity.merged_masks(parity.oracle_snapshot(o))); o.step()
+    r.sync()
+    assert np.array_equal(pb(envs.observations.numpy()), pb(o.observations))
+    assert np.array_equal(envs.rewards.numpy(), o.rewards)
     with pytest.raises(RuntimeError):
         envs.reset(123, 3, 4, cog.Difficulty.EASY, 100, False)  # generate_map_failure
     with pytest.raises(ValueError):
