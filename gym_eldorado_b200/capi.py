@@ -41,6 +41,8 @@ SYMBOLS = {
     "cog_sampler_sample_host": (_int, [_vp, _vp]),
     "cog_sampler_actions": (_int, [_vp, _P(_vp)]),
     "cog_sampler_read_actions": (_int, [_vp, _vp, _sz]),
+    "cog_sampler_sample_host_io": (_int, [_vp, _vp, _vp]),
+    "cog_vec_step_host_io": (_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "cog_vec_run_fused": (_int, [_vp, _vp, _u64]),
     "cog_vec_run_fused_ex": (_int, [_vp, _vp, _u64, _int]),
     "cog_vec_merged_masks": (_int, [_vp, _vp]),
@@ -128,6 +130,14 @@ class VecHandle:
         assert actions.dtype == layout.action_dtype and actions.flags.c_contiguous and len(actions) == self.n
         check(self.L, self.L.cog_vec_step_host(self._h, actions.ctypes.data))
 
+    def step_host_io(self, actions, masks_out=None, rewards_out=None, dones_out=None, agents_out=None):
+        """step(host actions) + read-back of the selected masks / rewards / dones / agent_selection into
+        host arrays, copies and kernels pipelined chunk by chunk (pinned memory overlaps)."""
+        assert actions.dtype == layout.action_dtype and actions.flags.c_contiguous and len(actions) == self.n
+        ptr = lambda a: None if a is None else a.ctypes.data
+        check(self.L, self.L.cog_vec_step_host_io(self._h, actions.ctypes.data, ptr(masks_out), ptr(rewards_out),
+                                                  ptr(dones_out), ptr(agents_out)))
+
     def buffer(self, which):
         """(device pointer, itemsize, count) of an exported buffer."""
         p, item, cnt = _vp(), _sz(), _sz()
@@ -190,6 +200,12 @@ class SamplerHandle:
     def sample_host(self, masks):
         assert masks.dtype == layout.action_mask_dtype and masks.flags.c_contiguous and len(masks) == self.n
         check(self.L, self.L.cog_sampler_sample_host(self._s, masks.ctypes.data))
+
+    def sample_host_io(self, masks, actions_out):
+        """sample(host masks) with the sampled actions copied back into `actions_out`, pipelined."""
+        assert masks.dtype == layout.action_mask_dtype and masks.flags.c_contiguous and len(masks) == self.n
+        assert actions_out.dtype == layout.action_dtype and actions_out.flags.c_contiguous and len(actions_out) == self.n
+        check(self.L, self.L.cog_sampler_sample_host_io(self._s, masks.ctypes.data, actions_out.ctypes.data))
 
     def actions_ptr(self):
         p = _vp()

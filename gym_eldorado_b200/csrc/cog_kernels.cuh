@@ -61,11 +61,13 @@ __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed)
 }
 
 /* vec_cog_env<N>::step(actions): one step per env from `actions` (ActionData[n], 64-byte
- * records), auto-reset included; exports only the records the step touched. */
-__global__ void __launch_bounds__(BLOCK_THREADS, 6) k_step_single(Buffers B, Params prm, u64 n,
+ * records), auto-reset included; exports only the records the step touched.  Works on the
+ * envs [i0, n) (i0 a multiple of the warps per block): the host-buffer entry points run it
+ * chunk by chunk so that copies and kernels of different chunks overlap. */
+__global__ void __launch_bounds__(BLOCK_THREADS, 6) k_step_single(Buffers B, Params prm, u64 i0, u64 n,
                                                                   const u8 *__restrict__ actions_in) {
   const int lane = threadIdx.x & 31;
-  const u64 i = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  const u64 i = i0 + (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
   if (i >= n) return;
   Env E;
   env_load(E, B.hidden + i * COG_HID_WORDS, lane);

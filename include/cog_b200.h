@@ -132,6 +132,19 @@ COG_API int cog_sampler_sample_host(cog_sampler *s, const void *h_masks);
 COG_API int cog_sampler_actions(cog_sampler *s, void **d_ptr);
 COG_API int cog_sampler_read_actions(cog_sampler *s, void *h_dst, size_t nbytes);
 
+/* Host-buffer forms of sample() / step() for callers whose policy lives on the host (the
+ * reference's Python loop hands numpy arrays to vec_sampler.sample and vec_cog_env.step,
+ * include/pybind/vectorized.h:60-68,107-127, and reads the views afterwards).  One call =
+ * copy the inputs in, run, copy the results out, cut into two chunks (COG_IO_CHUNKS) on two
+ * internal streams so that H2D, kernel and D2H of different chunks overlap; the host buffers are complete when
+ * the call returns.  Pinned host memory is needed for the overlap (pageable memory works,
+ * serialised).  Any *_out pointer of cog_vec_step_host_io may be NULL.
+ *   h_masks / h_masks_out : ActionMask[n_envs]   h_actions / h_actions_out : ActionData[n_envs]
+ *   h_rewards_out : float[n_envs][4]   h_dones_out : bool[n_envs]   h_agents_out : uint8[n_envs] */
+COG_API int cog_sampler_sample_host_io(cog_sampler *s, const void *h_masks, void *h_actions_out);
+COG_API int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, void *h_rewards_out,
+                                 void *h_dones_out, void *h_agents_out);
+
 /* ThreadedRunner<N> replacement (include/runner.h:21-134): k_steps x
  * { sample(selected_action_masks); step(actions) } in ONE persistent kernel with
  * no host round trip; bit-identical to k_steps single sample+step calls.

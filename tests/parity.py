@@ -187,3 +187,41 @@ def run_fused_merged_parity(library, oracle_cls, n, seed, difficulty, max_steps,
     finally:
         c.close()
         o.close()
+
+
+def run_host_io_parity(library, oracle_cls, n, seed, difficulty, max_steps, steps, regime="A"):
+    """The pipelined host-buffer entry points (cog_sampler_sample_host_io, cog_vec_step_host_io)
+    driven like the reference's Python loop — masks and actions only ever live in host arrays —
+    against the oracle."""
+    o = oracle_cls(n, seed)
+    c = Candidate(library, n, seed)
+    try:
+        o.reset(seed, 4, 3, difficulty, max_steps)
+        c.reset(seed, 4, 3, difficulty, max_steps)
+        masks = c.vec.read(layout.BUF_SELECTED_MASKS)
+        actions = np.zeros(n, dtype=layout.action_dtype)
+        rewards = np.zeros((n, 4), dtype=np.float32)
+        dones = np.zeros(n, dtype=np.bool_)
+        agents = np.zeros(n, dtype=np.uint8)
+        n_done = 0
+        for s in range(steps):
+            if regime == "M":
+                m = merged_masks(c.snapshot())
+                o.sample(m)
+            else:
+                m = masks
+                o.sample()
+            c.smp.sample_host_io(m, actions)
+            assert np.array_equal(pb(actions), pb(o.actions)), "step %d: actions" % s
+            o.step()
+            c.vec.step_host_io(actions, masks, rewards, dones, agents)
+            assert np.array_equal(pb(masks), pb(o.selected_action_masks)), "step %d: masks" % s
+            assert np.array_equal(rewards, o.rewards) and np.array_equal(dones, o.dones), "step %d" % s
+            assert np.array_equal(agents, o.agent_selection), "step %d: agent_selection" % s
+            n_done += int(dones.sum())
+        bad = first_mismatch(c.snapshot(), oracle_snapshot(o))
+        assert bad is None, bad
+        return n_done
+    finally:
+        c.close()
+        o.close()

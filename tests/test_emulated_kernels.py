@@ -53,3 +53,7 @@ def test_emulated_fused_merged_masks(emu, oracle_cls):
     st = parity.run_fused_merged_parity(emu, oracle_cls, 12, 777, layout.EASY, 60, (1, 0, 37, 400))
     assert st["episodes"] > 0 and st["travelled_hexes"] > 0 and st["cards_added"] > 0
     assert st["env_steps"] == 12 * 438
+
+
+def test_emulated_host_io(emu, oracle_cls):
+    assert parity.run_host_io_parity(emu, oracle_cls, 10, 5, layout.HARD, 6, 120) > 0

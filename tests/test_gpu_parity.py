@@ -140,3 +140,11 @@ def test_fused_merged_masks(cuda_lib, oracle_cls, n, difficulty, max_steps, n_pl
                                         n_players=n_players)
     assert st["episodes"] > 0 and st["travelled_hexes"] > 0
     assert st["env_steps"] == n * 361
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,regime", [(20000, "A"), (9001, "M")])
+def test_host_io_pipeline(cuda_lib, oracle_cls, n, regime):
+    """sample / step through HOST buffers with chunked copy/compute overlap (several chunks,
+    a ragged last one) == the oracle at every step."""
+    assert parity.run_host_io_parity(cuda_lib, oracle_cls, n, 99, layout.HARD, 10, 150, regime) > 0
