@@ -230,15 +230,32 @@ __device__ __forceinline__ u32 nth_set_bit_warp(u32 v, u32 j, int lane) {
 /* one +60 degree step in half-hex axial coordinates: (x, y) -> (-y, x + y)
  * (rotate_point src/map.cpp:17-37 through src/geometry.cpp:3-17; exact on the
  * half lattice).  `times` keeps C remainder semantics like the reference. */
-__device__ __forceinline__ void rotate_pt(int &x, int &y, int times) {
+/* The six rotations as integer matrices (a b; c d): k steps of (x, y) -> (-y, x + y).
+ * Packed 2 bits per coefficient (value + 1) so that one constant serves all of them. */
+struct rot6 { int a, b, c, d; };
+__device__ __forceinline__ rot6 rot_matrix(int times) {
   int t = times % 6;
   if (t < 0) t += 6;
-  for (int k = 0; k < t; ++k) {
-    int nx = -y, ny = x + y;
-    x = nx;
-    y = ny;
-  }
+  /* t:      0         1          2          3          4          5
+   * a b   1  0     0 -1      -1 -1      -1  0       0  1       1  1
+   * c d   0  1     1  1       1  0       0 -1      -1 -1      -1  0   */
+  const u32 A = 0x2 | (0x1 << 2) | (0x0 << 4) | (0x0 << 6) | (0x1 << 8) | (0x2 << 10);
+  const u32 Bc = 0x1 | (0x0 << 2) | (0x0 << 4) | (0x1 << 6) | (0x2 << 8) | (0x2 << 10);
+  const u32 C = 0x1 | (0x2 << 2) | (0x2 << 4) | (0x1 << 6) | (0x0 << 8) | (0x0 << 10);
+  const u32 D = 0x2 | (0x2 << 2) | (0x1 << 4) | (0x0 << 6) | (0x0 << 8) | (0x1 << 10);
+  rot6 m;
+  m.a = (int)((A >> (2 * t)) & 3u) - 1;
+  m.b = (int)((Bc >> (2 * t)) & 3u) - 1;
+  m.c = (int)((C >> (2 * t)) & 3u) - 1;
+  m.d = (int)((D >> (2 * t)) & 3u) - 1;
+  return m;
 }
+__device__ __forceinline__ void rot_apply(const rot6 &m, int &x, int &y) {
+  const int nx = m.a * x + m.b * y, ny = m.c * x + m.d * y;
+  x = nx;
+  y = ny;
+}
+__device__ __forceinline__ void rotate_pt(int &x, int &y, int times) { rot_apply(rot_matrix(times), x, y); }
 
 /* ------------------------------------------------------------ env in regs */
 /* parameters of vec_cog_env::reset(seed, ...) — identical for every env of a handle */
@@ -832,10 +849,11 @@ __device__ __forceinline__ int bg_add_random_piece(BoardScratch &sc, BoardState 
       int x, y, rot_add;
       bg_conn_entry(sc, host, kind, n_alt, lane, x, y, rot_add);
       const int r0 = first_opt + rot_add; /* only the FIRST rotation option is tested */
+      const rot6 m = rot_matrix(r0);
       ok = true;
       for (int h = 0; h < pm.n_hexes; ++h) {
         int hx = co[h].x, hy = co[h].y;
-        rotate_pt(hx, hy, r0);
+        rot_apply(m, hx, hy);
         const u32 b = occ_index(hx + x, hy + y);
         if ((sc.occ[b >> 5] >> (b & 31)) & 1u) { ok = false; break; }
       }
@@ -974,25 +992,37 @@ __device__ __forceinline__ int bg_finalize(const BoardScratch &sc, const BoardSt
     __syncwarp();
   }
   if (__any_sync(COG_FULL, bad)) return -3;
+  /* 16-byte chunk c covers observation bytes [16 c, 16 c + 16) = the 7-byte records of <= 4
+   * consecutive cells starting at cell0 = 16 c / 7, the first one cut off by `phase` bytes.
+   * A cell's record is one 56-bit value (byte f = feature f): n_required in byte
+   * requirement + 1, is_end in byte 6; it is shifted to its place in the 128-bit chunk. */
   uint4 *m4 = reinterpret_cast<uint4 *>(mapobs);
+  const u32 *gw = reinterpret_cast<const u32 *>(grid);
   for (int c = lane; c < COGL_MAP_BYTES / 16; c += 32) {
-    const int o = 16 * c, cell0 = o / 7;
-    u32 w[4] = {0, 0, 0, 0};
-    u32 codes = 0; /* the <= 4 cells this chunk touches */
-    for (int j = 0; j < 4; ++j)
-      if (cell0 + j < COGL_GRID_BYTES) codes |= (u32)grid[cell0 + j] << (8 * j);
+    const int o = 16 * c, cell0 = o / 7, phase = o - 7 * cell0;
+    const int w0 = cell0 >> 2;
+    const u32 lo_w = gw[w0], hi_w = w0 + 1 < COGL_GRID_BYTES / 4 ? gw[w0 + 1] : 0u;
+    const u32 codes = __funnelshift_r(lo_w, hi_w, 8 * (cell0 & 3)); /* the 4 cells' codes */
+    u64 lo = 0, hi = 0;
     if (codes) {
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const int cell = (o + j) / 7, f = (o + j) - 7 * cell;
-        const u32 code = (codes >> (8 * (cell - cell0))) & 0xffu;
-        u32 v = 0;
-        if (f == 6) v = (u32)hex_end(code);
-        else if (f >= 1 && hex_req(code) == f - 1) v = (u32)hex_n(code);
-        w[j >> 2] |= v << (8 * (j & 3));
+      for (int k = 0; k < 4; ++k) {
+        const u32 code = (codes >> (8 * k)) & 0xffu;
+        const u32 f = code & 7u; /* requirement + 1, 0 = none */
+        u64 v = (u64)((code >> 6) & 1u) << 48;
+        if (f) v |= (u64)((code >> 3) & 7u) << (8 * f);
+        const int off = 7 * k - phase; /* byte offset of the record inside the chunk, -6 .. 21 */
+        if (off < 0) {
+          lo |= v >> (8 * -off);
+        } else if (off < 8) {
+          lo |= v << (8 * off);
+          if (off > 1) hi |= v >> (8 * (8 - off));
+        } else if (off < 16) {
+          hi |= v << (8 * (off - 8));
+        }
       }
     }
-    m4[c] = make_uint4(w[0], w[1], w[2], w[3]);
+    m4[c] = make_uint4((u32)lo, (u32)(lo >> 32), (u32)hi, (u32)(hi >> 32));
   }
   return 0;
 }
