@@ -339,6 +339,30 @@ def main():
                               "merged legal masks" if merged else "selected_action_masks")}
             v2.close(); s2.close()
 
+    # the reference's own Python loop on DEVICE buffers (zero copy): sample(selected masks); step(actions),
+    # two single-step kernel launches per iteration, nothing crosses PCIe
+    api_loop = None
+    if not args.no_side:
+        masks_ptr = vec.buffer(layout.BUF_SELECTED_MASKS)[0]
+        act_ptr = smp.actions_ptr()
+        it = 200
+        for _ in range(10):
+            smp.sample_device(masks_ptr); vec.step_device(act_ptr)
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        a0.record()
+        for _ in range(it):
+            smp.sample_device(masks_ptr); vec.step_device(act_ptr)
+        a1.record()
+        barrier()
+        tm = torch.tensor([a0.elapsed_time(a1)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        api_loop = {"value": world * n * it / (float(tm.item()) * 1e-3), "unit": "env-steps/s",
+                    "us_per_iteration": float(tm.item()) * 1e3 / it,
+                    "api": "sampler.sample(envs.selected_action_masks); envs.step(sampler.get_actions()) on device "
+                           "buffers, k_sample + k_step_single per iteration, %d iterations" % it}
+
     # end to end through the reference-facing call shape with HOST buffers: every step
     # copies that step's inputs (masks for sample(), actions for step()) from pinned host
     # memory and reads the step's results back
@@ -418,7 +442,7 @@ def main():
                 "higher_is_better": True, "scaling": "strong" if WORKLOAD.get("n_envs_total") else "weak",
                 "vs_baseline": None,
                 "dtype": "u8/u32 integer (f32 exports)", "data": "synthetic", "config": cfg,
-                "roofline": roofline, "resets": resets, "side_workloads": side, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_timed,
+                "roofline": roofline, "resets": resets, "side_workloads": side, "device_api_loop": api_loop, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_timed,
                 "gpu_launches_total": launches, "clocks": clk,
                 "episode_stats": dict(zip(capi.STAT_NAMES, (int(x) for x in stats_t.tolist())))}
         print(json.dumps(line))

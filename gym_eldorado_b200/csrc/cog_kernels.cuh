@@ -64,7 +64,7 @@ __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed)
  * records), auto-reset included; exports only the records the step touched.  Works on the
  * envs [i0, n) (i0 a multiple of the warps per block): the host-buffer entry points run it
  * chunk by chunk so that copies and kernels of different chunks overlap. */
-__global__ void __launch_bounds__(BLOCK_THREADS, 6) k_step_single(Buffers B, Params prm, u64 i0, u64 n,
+__global__ void __launch_bounds__(BLOCK_THREADS, 8) k_step_single(Buffers B, Params prm, u64 i0, u64 n,
                                                                   const u8 *__restrict__ actions_in) {
   const int lane = threadIdx.x & 31;
   const u64 i = i0 + (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
