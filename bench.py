@@ -309,11 +309,18 @@ def main():
     side = None
     if not args.no_side:
         side = {}
-        for name, diffc, npl, max_steps, merged in (("regime_M_merged_masks", WORKLOAD["difficulty"], 4, 100000, True),
-                                                    ("reset_heavy_configs3", "HARD", 2, 8, False)):
+        # ... and the rollout writer: the same fused loops appending one 256-byte compact
+        # record per env-step to a device ring of `slots` time slots
+        for name, diffc, npl, max_steps, merged, slots in (
+                ("regime_M_merged_masks", WORKLOAD["difficulty"], 4, 100000, True, 0),
+                ("reset_heavy_configs3", "HARD", 2, 8, False, 0),
+                ("rollout_ring", WORKLOAD["difficulty"], 4, 100000, False, 256),
+                ("rollout_ring_regime_M", WORKLOAD["difficulty"], 4, 100000, True, 256)):
             v2 = capi.VecHandle(n, offset, local_rank, None, L)
             s2 = capi.SamplerHandle(n, WORKLOAD["seed"], offset, local_rank, None, L)
             v2.reset(WORKLOAD["seed"], npl, 3, DIFFICULTY[diffc], max_steps)
+            if slots:
+                v2.rollout_attach(slots)
             inner2, reps = 256, 5
             for _ in range(2):
                 v2.run_fused(s2, inner2, merged=merged)
@@ -337,6 +344,9 @@ def main():
                           "config": "%d envs per GPU, %d players, %s, max_steps %d, %d launches x %d iterations, %s" % (
                               n, npl, diffc, max_steps, reps, inner2,
                               "merged legal masks" if merged else "selected_action_masks")}
+            if slots:
+                side[name]["ring"] = "%d slots x %d envs x %d B per GPU" % (slots, n, layout.compact_dtype.itemsize)
+                side[name]["ring_write_GBs_per_gpu"] = (st2["env_steps"] / world) * layout.compact_dtype.itemsize / sec / 1e9
             v2.close(); s2.close()
 
     # the reference's own Python loop on DEVICE buffers (zero copy): sample(selected masks); step(actions),

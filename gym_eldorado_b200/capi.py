@@ -46,6 +46,9 @@ SYMBOLS = {
     "cog_vec_run_fused": (_int, [_vp, _vp, _u64]),
     "cog_vec_run_fused_ex": (_int, [_vp, _vp, _u64, _int]),
     "cog_vec_merged_masks": (_int, [_vp, _vp]),
+    "cog_vec_compact_obs": (_int, [_vp, _vp, _int]),
+    "cog_vec_rollout_attach": (_int, [_vp, _u32]),
+    "cog_vec_rollout_info": (_int, [_vp, _P(_vp), _P(_u32), _P(_u64)]),
     "cog_vec_stats": (_int, [_vp, _P(_u64), _sz]),
     "cog_vec_stats_reset": (_int, [_vp]),
     "cog_sync": (_int, [_vp]),
@@ -158,6 +161,34 @@ class VecHandle:
 
     def merged_masks_device(self, d_out_ptr):
         check(self.L, self.L.cog_vec_merged_masks(self._h, d_out_ptr))
+
+    def compact_obs_device(self, d_out_ptr=None, merged=True):
+        """One 256-byte compact record per env (layout.compact_dtype) to device memory, or to
+        the handle's BUF_COMPACT buffer when d_out_ptr is None."""
+        check(self.L, self.L.cog_vec_compact_obs(self._h, d_out_ptr, 1 if merged else 0))
+
+    def compact_obs(self, merged=True):
+        """Compact records of the current state as a host array."""
+        self.compact_obs_device(None, merged)
+        return self.read(layout.BUF_COMPACT)
+
+    def rollout_attach(self, n_slots):
+        """Every later run_fused appends one compact record per env-step to a device ring of
+        n_slots time slots; 0 detaches."""
+        check(self.L, self.L.cog_vec_rollout_attach(self._h, int(n_slots)))
+
+    def rollout_info(self):
+        """(device pointer, n_slots, steps recorded per env since attach)"""
+        p, t, c = _vp(), _u32(), _u64()
+        check(self.L, self.L.cog_vec_rollout_info(self._h, ctypes.byref(p), ctypes.byref(t), ctypes.byref(c)))
+        return p.value, t.value, c.value
+
+    def read_rollout(self):
+        """The whole ring as a host array [n_slots][n] of compact records."""
+        _, t, _ = self.rollout_info()
+        out = np.empty((t, self.n), dtype=layout.compact_dtype)
+        check(self.L, self.L.cog_vec_read(self._h, layout.BUF_ROLLOUT, out.ctypes.data, out.nbytes))
+        return out
 
     def stats(self):
         out = (_u64 * len(STAT_NAMES))()

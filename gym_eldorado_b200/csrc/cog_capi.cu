@@ -75,6 +75,10 @@ struct cog_vec {
   bool timed = false;
   void *act_staging = nullptr; /* device copy of host actions for cog_vec_step_host */
   void *merged = nullptr;      /* COG_BUF_MERGED_MASKS, allocated on first use */
+  void *compact = nullptr;     /* COG_BUF_COMPACT, allocated on first use */
+  uint8_t *ring = nullptr;     /* rollout ring [ring_slots][n] compact records (cog_vec_rollout_attach) */
+  uint32_t ring_slots = 0;
+  uint64_t ring_steps = 0;     /* env-steps per env recorded since attach; next slot = ring_steps % ring_slots */
   cudaStream_t io[2] = {nullptr, nullptr}; /* copy/compute pipeline of the *_host_io entry points */
   cudaEvent_t io_ev[4] = {nullptr, nullptr, nullptr, nullptr};
 };
@@ -169,6 +173,17 @@ uint64_t io_chunk(uint64_t n) {
 
 }  // namespace
 
+namespace {
+template <bool MERGED, bool ROLLOUT>
+void launch_fused(cog_vec *h, cog_sampler *s, unsigned grid, unsigned tail_grid, uint32_t k_steps, const cog::Rollout &R) {
+  auto hot = cog::k_step_fused<MERGED, ROLLOUT>;
+  auto tail = cog::k_step_tail<MERGED, ROLLOUT>;
+  COG_LAUNCH(hot, grid, cog::BLOCK_THREADS, 0, h->stream, h->B, h->prm, h->n, s->srng, s->actions, k_steps, R);
+  COG_LAUNCH(tail, tail_grid, cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm, h->n, s->srng,
+             s->actions, k_steps, R);
+}
+}  // namespace
+
 extern "C" {
 
 const char *cog_last_error(void) { return g_error.c_str(); }
@@ -216,12 +231,14 @@ int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device, void 
     }
   }
 #ifndef COG_EMU
-  CK(cudaFuncSetAttribute(cog::k_step_tail<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
+  CK(cudaFuncSetAttribute(cog::k_step_tail<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
+  CK(cudaFuncSetAttribute(cog::k_step_tail<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
+  CK(cudaFuncSetAttribute(cog::k_step_tail<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
+  CK(cudaFuncSetAttribute(cog::k_step_tail<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
   int per_sm = 0;
-  CK(cudaFuncSetAttribute(cog::k_step_tail<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_fused<false>, cog::BLOCK_THREADS, 0));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_fused<false, false>, cog::BLOCK_THREADS, 0));
   h->fused_blocks_per_sm = per_sm > 0 ? per_sm : 1;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_tail<false>, cog::BLOCK_THREADS, scratch_bytes()));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_tail<false, false>, cog::BLOCK_THREADS, scratch_bytes()));
   h->tail_blocks_per_sm = per_sm > 0 ? per_sm : 1;
 #endif
   COG_LAUNCH(cog::k_init, blocks_for(n), cog::BLOCK_THREADS, 0, h->stream, h->B, n);
@@ -237,7 +254,8 @@ int cog_vec_destroy(cog_vec *h) {
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
   void *ptrs[] = {h->B.hidden, h->B.grid, h->B.obs, h->B.masks, h->B.rewards,
-                  h->B.dones,  h->B.infos, h->B.agents, h->B.stats, h->B.err, h->B.park, h->act_staging, h->merged};
+                  h->B.dones,  h->B.infos, h->B.agents, h->B.stats, h->B.err, h->B.park, h->act_staging, h->merged,
+                  h->compact, h->ring};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   if (h->ev0) cudaEventDestroy(h->ev0);
@@ -311,6 +329,21 @@ int cog_vec_buffer(cog_vec *h, int which, void **d_ptr, size_t *itemsize, size_t
       CK(cudaMemsetAsync(h->merged, 0, h->n * COG_MASK_SIZE, h->stream));
     }
     p = h->merged; item = COG_MASK_SIZE; break;
+  case COG_BUF_GRID: p = h->B.grid; item = COG_GRID_BYTES; break;
+  case COG_BUF_COMPACT:
+    if (!h->compact) {
+      CK(cudaSetDevice(h->device));
+      CK(cudaMalloc(&h->compact, h->n * COG_COMPACT_SIZE));
+      CK(cudaMemsetAsync(h->compact, 0, h->n * COG_COMPACT_SIZE, h->stream));
+    }
+    p = h->compact; item = COG_COMPACT_SIZE; break;
+  case COG_BUF_ROLLOUT:
+    if (!h->ring) return fail(COG_ERR_INVALID, "no rollout ring attached");
+    p = h->ring; item = COG_COMPACT_SIZE;
+    if (d_ptr) *d_ptr = p;
+    if (itemsize) *itemsize = item;
+    if (count) *count = (size_t)h->n * h->ring_slots;
+    return COG_OK;
   default: return fail(COG_ERR_INVALID, "unknown buffer id");
   }
   if (d_ptr) *d_ptr = p;
@@ -477,6 +510,52 @@ int cog_vec_run_fused(cog_vec *h, cog_sampler *s, uint64_t k_steps) {
   return cog_vec_run_fused_ex(h, s, k_steps, COG_MASKS_SELECTED);
 }
 
+int cog_vec_compact_obs(cog_vec *h, void *d_out, int mask_mode) {
+  if (!h) return fail(COG_ERR_INVALID, "NULL argument");
+  if (mask_mode != COG_MASKS_SELECTED && mask_mode != COG_MASKS_MERGED) return fail(COG_ERR_INVALID, "unknown mask mode");
+  if (!h->seeded) return fail(COG_ERR_NOT_RESET, "compact observation before reset()");
+  CK(cudaSetDevice(h->device));
+  if (!d_out) {
+    int rc = cog_vec_buffer(h, COG_BUF_COMPACT, &d_out, nullptr, nullptr);
+    if (rc) return rc;
+  }
+  COG_LAUNCH(cog::k_compact_obs, blocks_for(h->n), cog::BLOCK_THREADS, 0, h->stream, h->B, h->prm, h->n,
+             (uint8_t *)d_out, mask_mode == COG_MASKS_MERGED ? 1 : 0);
+  g_launches++;
+  CK(cudaGetLastError());
+  return COG_OK;
+}
+
+int cog_vec_rollout_attach(cog_vec *h, uint32_t n_slots) {
+  if (!h) return fail(COG_ERR_INVALID, "NULL handle");
+  CK(cudaSetDevice(h->device));
+  CK(cudaStreamSynchronize(h->stream));
+  if (h->ring) {
+    CK(cudaFree(h->ring));
+    h->ring = nullptr;
+  }
+  h->ring_slots = 0;
+  h->ring_steps = 0;
+  if (!n_slots) return COG_OK; /* detached */
+  const size_t bytes = (size_t)n_slots * h->n * COG_COMPACT_SIZE;
+  cudaError_t e = cudaMalloc((void **)&h->ring, bytes);
+  if (e != cudaSuccess) {
+    h->ring = nullptr;
+    return cuda_fail(e, "cudaMalloc (rollout ring)");
+  }
+  CK(cudaMemsetAsync(h->ring, 0, bytes, h->stream));
+  h->ring_slots = n_slots;
+  return COG_OK;
+}
+
+int cog_vec_rollout_info(cog_vec *h, void **d_ring, uint32_t *n_slots, uint64_t *steps_recorded) {
+  if (!h) return fail(COG_ERR_INVALID, "NULL handle");
+  if (d_ring) *d_ring = h->ring;
+  if (n_slots) *n_slots = h->ring_slots;
+  if (steps_recorded) *steps_recorded = h->ring_steps;
+  return COG_OK;
+}
+
 int cog_vec_merged_masks(cog_vec *h, void *d_out) {
   if (!h) return fail(COG_ERR_INVALID, "NULL argument");
   if (!h->seeded) return fail(COG_ERR_NOT_RESET, "merged masks before reset()");
@@ -503,24 +582,30 @@ int cog_vec_run_fused_ex(cog_vec *h, cog_sampler *s, uint64_t k_steps, int mask_
   unsigned grid = blocks_for(h->n);
   const unsigned resident = (unsigned)(h->sm_count * h->fused_blocks_per_sm);
   if (grid > resident) grid = resident;
+  cog::Rollout R{};
+  if (h->ring) {
+    R.ring = h->ring;
+    R.n = h->n;
+    R.T = h->ring_slots;
+    R.slot0 = (uint32_t)(h->ring_steps % h->ring_slots);
+    R.t0 = (uint32_t)h->ring_steps;
+  }
   time_begin(h);
   if (k_steps) {
-    if (mask_mode == COG_MASKS_MERGED)
-      COG_LAUNCH(cog::k_step_fused<true>, grid, cog::BLOCK_THREADS, 0, h->stream, h->B, h->prm, h->n, s->srng,
-                 s->actions, (uint32_t)k_steps);
-    else
-      COG_LAUNCH(cog::k_step_fused<false>, grid, cog::BLOCK_THREADS, 0, h->stream, h->B, h->prm, h->n, s->srng,
-                 s->actions, (uint32_t)k_steps);
-    /* the envs whose episode ended (exits at once when there are none); its own resident grid */
+    /* the envs whose episode ended go to the tail kernel (exits at once when there are none);
+     * it has its own resident grid */
     unsigned tail_grid = blocks_for(h->n);
     const unsigned tail_resident = (unsigned)(h->sm_count * h->tail_blocks_per_sm);
     if (tail_grid > tail_resident) tail_grid = tail_resident;
-    if (mask_mode == COG_MASKS_MERGED)
-      COG_LAUNCH(cog::k_step_tail<true>, tail_grid, cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm,
-                 h->n, s->srng, s->actions);
-    else
-      COG_LAUNCH(cog::k_step_tail<false>, tail_grid, cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm,
-                 h->n, s->srng, s->actions);
+    const bool merged = mask_mode == COG_MASKS_MERGED;
+    if (h->ring) {
+      if (merged) launch_fused<true, true>(h, s, grid, tail_grid, (uint32_t)k_steps, R);
+      else launch_fused<false, true>(h, s, grid, tail_grid, (uint32_t)k_steps, R);
+      h->ring_steps += k_steps;
+    } else {
+      if (merged) launch_fused<true, false>(h, s, grid, tail_grid, (uint32_t)k_steps, R);
+      else launch_fused<false, false>(h, s, grid, tail_grid, (uint32_t)k_steps, R);
+    }
     g_launches += 2;
   }
   time_end(h);

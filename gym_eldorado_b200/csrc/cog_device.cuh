@@ -469,6 +469,69 @@ __device__ __forceinline__ void export_dynamic(const Env &E, const Buffers &B, u
         (u8)getb(E.info_steps, rel(E, lane));
 }
 
+/* ---------------------------------------------------------- compact records */
+/* ring of compact records (layout: cog_layout.h) that a fused launch appends to, one record
+ * per env-step: step t of env i lives at ring + ((t % T) * n + i) * COGL_CR_SIZE */
+struct Rollout {
+  u8 *ring;
+  u64 n;     /* envs per slot */
+  u32 T;     /* slots */
+  u32 slot0; /* slot of the launch's first step */
+  u32 t0;    /* index of that step since the ring was attached */
+};
+
+/* cells 0..27: the state the current agent acts from, the mask heads its action is sampled
+ * from and the action itself.  Lane c assembles cell c; one 8-byte store per lane. */
+__device__ __forceinline__ void compact_store_pre(u8 *rec, const Env &E, const Params &prm, u32 play, u32 spec,
+                                                  u32 rem, u32 ms, u32 act, u32 a_shop, int lane) {
+  const int np = (int)prm.n_players < 4 ? (int)prm.n_players : 4;
+  u32 g = 0; /* the cell of the hex grid the player stands on (Map::get_from_array indexing) */
+  if (lane < np)
+    g = (u32)((loc_x(E.ploc) - E.minx) / 2 + 1) | ((u32)((loc_y(E.ploc) - E.miny) / 2 + 1) << 8);
+  const u32 g01 = bcast(g, 0) | (bcast(g, 1) << 16), g23 = bcast(g, 2) | (bcast(g, 3) << 16);
+  uint2 c = make_uint2(0u, 0u);
+  if (lane >= 1 && lane <= 21) {
+    c.x = (E.draw & 0xffu) | ((E.hand & 0xffu) << 8) | ((E.active & 0xffu) << 16) | (E.played << 24);
+    c.y = (E.discard & 0xffu) | (lane <= 18 ? (E.shop & 0xffu) << 8 : 0u);
+  } else {
+    switch (lane) {
+    case 0:
+      c.x = E.agent | (E.phase << 8) | (((u32)E.res[0] & 0xffffu) << 16);
+      c.y = ((u32)E.res[1] & 0xffffu) | (((u32)E.res[2] & 0xffffu) << 16);
+      break;
+    case 22: c.x = act; c.y = a_shop; break;
+    case 23: c.x = play; c.y = rem; break;
+    case 24: c.x = ms; c.y = spec; break;
+    case 25: c.x = g01; c.y = g23; break;
+    case 26: c.x = E.turn; break;
+    default: break;
+    }
+  }
+  if (lane < COGL_CR_PRE_CELLS) reinterpret_cast<uint2 *>(rec)[lane] = c;
+}
+/* cells 28..31 (one 32-byte sector): the outcome of the step taken from that state */
+__device__ __forceinline__ void compact_store_post(u8 *rec, u32 done, u32 filled, u32 r01lo, u32 r01hi, u32 r23lo,
+                                                   u32 r23hi, u32 t, int lane) {
+  uint2 c = make_uint2(0u, 0u);
+  if (lane == 28) c.x = done | (filled << 8);
+  if (lane == 29) { c.x = r01lo; c.y = r01hi; }
+  if (lane == 30) { c.x = r23lo; c.y = r23hi; }
+  if (lane == 31) c.x = t;
+  if (lane >= COGL_CR_PRE_CELLS) reinterpret_cast<uint2 *>(rec)[lane] = c;
+}
+/* the rewards of an episode end (get_reward src/environment.cpp:281-288) into the record of
+ * the step that ended it.  Call after env_finish_episode (absolute player order). */
+__device__ __forceinline__ void compact_store_rewards(u8 *rec, const Env &E, const Params &prm, int lane) {
+  const int np = (int)prm.n_players < 4 ? (int)prm.n_players : 4;
+  const bool won = lane < 4 && (E.pf & PFL_WON);
+  const int n_winners = __popc(__ballot_sync(COG_FULL, won));
+  u32 r = 0;
+  if (lane < np) r = __float_as_uint((float)((int)prm.n_players * (won ? 1 : 0) - n_winners));
+  const u32 r0 = bcast(r, 0), r1 = bcast(r, 1), r2 = bcast(r, 2), r3 = bcast(r, 3);
+  if (lane == 29) *reinterpret_cast<uint2 *>(rec + COGL_CR_REWARDS) = make_uint2(r0, r1);
+  if (lane == 30) *reinterpret_cast<uint2 *>(rec + COGL_CR_REWARDS + 8) = make_uint2(r2, r3);
+}
+
 /* ------------------------------------------------------------------- decks */
 __device__ __forceinline__ int res_get(const Env &E, int k) {
   return k == 0 ? E.res[0] : (k == 1 ? E.res[1] : E.res[2]);

@@ -117,23 +117,36 @@ __device__ __forceinline__ void store_action(u8 *actions_out, u64 i, u32 act, u3
 /* MERGED = false: actions sampled from selected_action_masks (the reference's own flow,
  * "regime A": only `play` ever has a choice).  MERGED = true: from the merged legal mask of
  * the current agent ("regime M": moves, purchases, removals, wins — every branch of step). */
-template <bool MERGED>
+/* ROLLOUT = true: a compact record of the state, the mask heads sampled from, the action and
+ * the outcome goes to `rec` — two coalesced stores per env-step. */
+template <bool MERGED, bool ROLLOUT>
 __device__ __forceinline__ u32 sample_and_step(Env &E, u32 &sr, u32 &act, u32 &a_shop, const Params &prm,
-                                               const Buffers &B, u64 i, bool &obs_pending, int lane) {
+                                               const Buffers &B, u64 i, bool &obs_pending, u8 *rec, u32 t,
+                                               int lane) {
+  u32 status;
   if (MERGED) {
     u32 rem, ms;
     merged_heads(E, lane, rem, ms);
     sample_action(sr, E.Splay, spec_of(E.Splay), rem, ms, act, a_shop, lane);
-    return env_step<false, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
+    if (ROLLOUT) compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), rem, ms, act, a_shop, lane);
+    status = env_step<false, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
+  } else {
+    const bool play_only = sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane);
+    if (ROLLOUT) compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane);
+    if (play_only) status = env_step<true, true>(E, act, 0, prm, B, i, obs_pending, lane);
+    else status = env_step<true, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
   }
-  if (sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane))
-    return env_step<true, true>(E, act, 0, prm, B, i, obs_pending, lane);
-  return env_step<true, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
+  /* rewards stay zero here: the kernel that finishes the episode fills them in */
+  if (ROLLOUT) compact_store_post(rec, status & 1u, 1u, 0u, 0u, 0u, 0u, t, lane);
+  return status;
+}
+__device__ __forceinline__ u8 *rollout_rec(const Rollout &R, u32 slot, u64 i) {
+  return R.ring + ((u64)slot * R.n + i) * COGL_CR_SIZE;
 }
 
-template <bool MERGED>
+template <bool MERGED, bool ROLLOUT>
 __global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step_fused(Buffers B, Params prm, u64 n, u32 *srng,
-                                                                             u8 *actions_out, u32 k_steps) {
+                                                                             u8 *actions_out, u32 k_steps, Rollout R) {
   const int lane = threadIdx.x & 31;
 #ifdef COG_UNIFORM_PROOF
   /* EXPERIMENT, off by default.  With the warp index taken through a shuffle from a fixed
@@ -157,8 +170,14 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step_fused(Bu
     u32 act = 0, a_shop = 0, status = 0;
     bool obs_pending = false;
     u32 k = k_steps;
+    u32 slot = R.slot0, t = R.t0;
     do {
-      status = sample_and_step<MERGED>(E, sr, act, a_shop, prm, B, i, obs_pending, lane);
+      status = sample_and_step<MERGED, ROLLOUT>(E, sr, act, a_shop, prm, B, i, obs_pending,
+                                                ROLLOUT ? rollout_rec(R, slot, i) : nullptr, t, lane);
+      if (ROLLOUT) {
+        ++t;
+        if (++slot == R.T) slot = 0;
+      }
       --k;
     } while (k && !(status & 1u));
     steps_done += k_steps - k;
@@ -183,8 +202,9 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step_fused(Bu
 
 /* second kernel of a fused launch: the envs whose episode ended in k_step_fused.
  * park[0] counts envs ever parked, park[1] envs ever picked up again. */
-template <bool MERGED>
-__global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Buffers B, Params prm, u64 n, u32 *srng, u8 *actions_out) {
+template <bool MERGED, bool ROLLOUT>
+__global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Buffers B, Params prm, u64 n, u32 *srng,
+                                                                             u8 *actions_out, u32 k_steps, Rollout R) {
   const int lane = threadIdx.x & 31;
   if (*(volatile unsigned *)&B.park[0] == *(volatile unsigned *)&B.park[1]) return; /* nothing parked */
   const u64 warp0 = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
@@ -202,13 +222,28 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Bu
     u32 act = 0, a_shop = 0, status = 1;
     bool obs_pending = false;
     const u32 k = parked - 1u;
+    /* the step that parked the env was step k_steps - parked of this launch */
+    u32 slot = 0, t = 0;
+    u8 *rec = nullptr;
+    if (ROLLOUT) {
+      const u32 j_done = k_steps - parked;
+      slot = (u32)(((u64)R.slot0 + j_done) % R.T);
+      t = R.t0 + j_done;
+      rec = rollout_rec(R, slot, i);
+    }
     for (u32 j = 0;; ++j) {
       if (status & 1u) { /* rewards / Info / aggregates, then auto-reset: the RNG stream continues */
         env_finish_episode(E, prm, B, i, lane);
+        if (ROLLOUT) compact_store_rewards(rec, E, prm, lane);
         env_reset(E, prm, B, i, sc, lane);
       }
       if (j == k) break;
-      status = sample_and_step<MERGED>(E, sr, act, a_shop, prm, B, i, obs_pending, lane);
+      if (ROLLOUT) {
+        ++t;
+        if (++slot == R.T) slot = 0;
+        rec = rollout_rec(R, slot, i);
+      }
+      status = sample_and_step<MERGED, ROLLOUT>(E, sr, act, a_shop, prm, B, i, obs_pending, rec, t, lane);
     }
     steps_done += k;
     if (obs_pending) env_update_observation(E, (int)E.agent, 0, E.cpc, lane);
@@ -237,6 +272,20 @@ __global__ void k_merged_masks(Buffers B, u64 n, u8 *out) {
   u32 rem, ms;
   merged_heads(E, lane, rem, ms);
   export_mask(out + i * COGL_MASK_SIZE, E.Splay, spec_of(E.Splay), rem, ms, lane);
+}
+
+/* one compact record per env for its current state; merged = which mask heads */
+__global__ void k_compact_obs(Buffers B, Params prm, u64 n, u8 *out, int merged) {
+  const int lane = threadIdx.x & 31;
+  const u64 i = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  if (i >= n) return;
+  Env E;
+  env_load(E, B.hidden + i * COG_HID_WORDS, lane);
+  u32 rem = E.Srem, ms = E.Sms;
+  if (merged) merged_heads(E, lane, rem, ms);
+  u8 *rec = out + i * COGL_CR_SIZE;
+  compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), rem, ms, 0u, 0u, lane);
+  compact_store_post(rec, 0u, 0u, 0u, 0u, 0u, 0u, 0u, lane);
 }
 
 /* vec_action_sampler<N>::sample include/vec_sampler.h:14-21 on ActionMask[n] records:

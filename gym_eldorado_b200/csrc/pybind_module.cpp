@@ -137,6 +137,7 @@ public:
     }
     if (vec) ck(cog_vec_read(vec->h, which, arr.mutable_data(), itemsize * count));
     else ck(cog_sampler_read_actions(sampler->s, arr.mutable_data(), itemsize * count));
+    if (out.is_none() && shape.size() == 3) return arr.attr("reshape")(shape[0], shape[1]);
     return arr;
   }
 };
@@ -203,6 +204,9 @@ public:
     case COG_BUF_SELECTED_MASKS:
     case COG_BUF_MERGED_MASKS: b.np_dtype = layout_dtype("action_mask_dtype"); break;
     case COG_BUF_INFOS: b.np_dtype = layout_dtype("info_dtype"); break;
+    case COG_BUF_COMPACT:
+    case COG_BUF_ROLLOUT: b.np_dtype = layout_dtype("compact_dtype"); break;
+    case COG_BUF_GRID: b.np_dtype = py::dtype("2304u1"); break;
     default: break;
     }
     if (which == COG_BUF_REWARDS) {
@@ -211,6 +215,8 @@ public:
       b.np_dtype = py::dtype("bool"); b.typestr = "|b1"; b.shape = {(int64_t)n}; b.dl = {kDLBool, 8, 1};
     } else if (which == COG_BUF_AGENT_SELECTION) {
       b.np_dtype = py::dtype("uint8"); b.typestr = "|u1"; b.shape = {(int64_t)n}; b.dl = {kDLUInt, 8, 1};
+    } else if (which == COG_BUF_ROLLOUT) { /* time-major [n_slots][n] records */
+      b.typestr = "|u1"; b.shape = {(int64_t)(b.count / n), (int64_t)n, (int64_t)b.itemsize}; b.dl = {kDLUInt, 8, 1};
     } else {
       b.typestr = "|u1"; b.shape = {(int64_t)n, (int64_t)b.itemsize}; b.dl = {kDLUInt, 8, 1};
     }
@@ -362,6 +368,28 @@ PYBIND11_MODULE(COG_MODULE_NAME, m) {
            "not in the reference: the merged legal mask of each env's current agent (play / play_special from "
            "selected_action_masks; move / get_from_shop / remove from observations.player_data[agent].action_mask), "
            "recomputed on every call into one persistent device buffer")
+      .def_property_readonly("hex_grid", [](const VecEnv &e) { return e.view(COG_BUF_GRID); },
+           "not in the reference: the board as one byte per hex, uint8[n][48*48] (bits 0-2 requirement + 1, "
+           "bits 3-5 n_required, bit 6 is_end); layout.grid_to_map() expands it to observations.shared.map")
+      .def("compact_observations",
+           [](const VecEnv &e, bool merged) {
+             ck(cog_vec_compact_obs(e.own->h, nullptr, merged ? COG_MASKS_MERGED : COG_MASKS_SELECTED));
+             return e.view(COG_BUF_COMPACT);
+           },
+           py::arg("merged_masks") = true,
+           "not in the reference: one 256-byte record per env with everything the current agent acts on "
+           "(layout.compact_dtype), recomputed on every call into one persistent device buffer")
+      .def("attach_rollout", [](VecEnv &e, uint32_t n_slots) { ck(cog_vec_rollout_attach(e.own->h, n_slots)); },
+           py::arg("n_slots"),
+           "not in the reference: every later runner.run() appends one compact record per env-step (state, "
+           "mask sampled from, action, done, rewards) to a device ring [n_slots][n]; 0 detaches")
+      .def_property_readonly("rollout", [](const VecEnv &e) { return e.view(COG_BUF_ROLLOUT); })
+      .def_property_readonly("rollout_steps",
+                             [](const VecEnv &e) {
+                               uint64_t steps = 0;
+                               ck(cog_vec_rollout_info(e.own->h, nullptr, nullptr, &steps));
+                               return steps;
+                             })
       .def("sync", [](VecEnv &e) { ck(cog_sync(e.own->h)); })
       .def("episode_stats", &VecEnv::stats)
       .def("reset_episode_stats", [](VecEnv &e) { ck(cog_vec_stats_reset(e.own->h)); });

@@ -87,8 +87,42 @@ info_dtype = np.dtype({
     "itemsize": 192,
 })
 
+# Not in the reference: the compact record (include/cog_b200.h, cog_vec_compact_obs) — the
+# current agent's view of one env in 256 bytes, and the element of the rollout ring.
+compact_card_dtype = np.dtype({
+    "names": ["draw", "hand", "active", "played", "discard", "shop"],
+    "formats": [np.uint8] * 6,
+    "offsets": [0, 1, 2, 3, 4, 5],
+    "itemsize": 8,
+})
+compact_dtype = np.dtype({
+    "names": ["agent_selection", "phase", "resources_x2", "cards", "action", "mask_play", "mask_remove",
+              "mask_move_shop", "mask_play_special", "loc", "turn_counter", "done", "filled", "rewards", "t"],
+    "formats": [np.uint8, np.uint8, (np.uint16, (N_RESOURCETYPES,)), (compact_card_dtype, (N_CARDTYPES,)),
+                (np.uint8, (5,)), np.uint32, np.uint32, np.uint32, np.uint32, (np.uint8, (MAX_N_PLAYERS, 2)),
+                np.uint32, np.uint8, np.uint8, (np.float32, (MAX_N_PLAYERS,)), np.uint32],
+    "offsets": [0, 1, 2, 8, 176, 184, 188, 192, 196, 200, 208, 224, 225, 232, 248],
+    "itemsize": 256,
+})
+GRID_BYTES = GRIDSIZE * GRIDSIZE
+
+
+def grid_to_map(grid):
+    """uint8[..., 48*48] hex codes (BUF_GRID) -> uint8[..., 48, 48, 7] map observation
+    (Map::finalize, reference src/map.cpp:389-405; feature 0 is never written)."""
+    g = np.asarray(grid, dtype=np.uint8).reshape(grid.shape[:-1] + (GRIDSIZE, GRIDSIZE))
+    out = np.zeros(g.shape + (N_MAP_FEATURES,), dtype=np.uint8)
+    f = g & 7
+    nreq = (g >> 3) & 7
+    for k in range(1, 7):
+        out[..., k] = np.where(f == k, nreq, 0)
+    out[..., 6] |= (g >> 6) & 1
+    return out
+
+
 # Which exported buffer is which (shared with include/cog_b200.h: enum cog_buffer)
-BUF_OBS, BUF_SELECTED_MASKS, BUF_REWARDS, BUF_DONES, BUF_INFOS, BUF_AGENT_SELECTION, BUF_MERGED_MASKS = range(7)
+(BUF_OBS, BUF_SELECTED_MASKS, BUF_REWARDS, BUF_DONES, BUF_INFOS, BUF_AGENT_SELECTION, BUF_MERGED_MASKS,
+ BUF_GRID, BUF_COMPACT, BUF_ROLLOUT) = range(10)
 
 BUFFER_DTYPES = {
     BUF_OBS: obs_dtype,
@@ -98,6 +132,9 @@ BUFFER_DTYPES = {
     BUF_INFOS: info_dtype,
     BUF_AGENT_SELECTION: np.dtype(np.uint8),
     BUF_MERGED_MASKS: action_mask_dtype,
+    BUF_GRID: np.dtype((np.uint8, (GRID_BYTES,))),
+    BUF_COMPACT: compact_dtype,
+    BUF_ROLLOUT: compact_dtype,
 }
 
 

@@ -36,6 +36,9 @@ using std::min;
 
 struct uint4 { uint32_t x, y, z, w; };
 static inline uint4 make_uint4(uint32_t x, uint32_t y, uint32_t z, uint32_t w) { return uint4{x, y, z, w}; }
+struct uint2 { uint32_t x, y; };
+static inline uint2 make_uint2(uint32_t x, uint32_t y) { return uint2{x, y}; }
+static inline uint32_t __float_as_uint(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
 struct emu_dim3 { unsigned x = 1, y = 1, z = 1; };
 static emu_dim3 threadIdx, blockIdx, blockDim, gridDim;
 

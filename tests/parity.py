@@ -225,3 +225,98 @@ def run_host_io_parity(library, oracle_cls, n, seed, difficulty, max_steps, step
     finally:
         c.close()
         o.close()
+
+
+def _bits(a):
+    a = np.asarray(a).astype(np.uint64)
+    return (a << np.arange(a.shape[1], dtype=np.uint64)).sum(axis=1).astype(np.uint32)
+
+
+def compact_expected(o, merged, n_players=4):
+    """The compact record (include/cog_b200.h, cog_vec_compact_obs) of every env's current
+    state, restated from the oracle's reference-layout buffers; player positions and the
+    turn counter (which the reference never exports) from the oracle's hidden state."""
+    snap = oracle_snapshot(o)
+    n = o.n
+    idx = np.arange(n)
+    ag = snap["agent_selection"]
+    obs = snap["observations"]
+    r = np.zeros(n, dtype=layout.compact_dtype)
+    r["agent_selection"] = ag
+    r["phase"] = obs["shared"]["phase"]
+    r["resources_x2"] = np.round(obs["shared"]["current_resources"] * 2).astype(np.uint16)
+    pd = obs["player_data"][idx, ag]
+    for name in ("draw", "hand", "active", "played", "discard"):
+        r["cards"][name] = pd["obs"][name]
+    r["cards"]["shop"][:, :layout.N_BUYABLETYPES] = obs["shared"]["shop"]
+    m = merged_masks(snap) if merged else snap["selected_action_masks"]
+    r["mask_play"] = _bits(m["play"])
+    r["mask_play_special"] = _bits(m["play_special"])
+    r["mask_remove"] = _bits(m["remove"])
+    r["mask_move_shop"] = _bits(m["move"]) | (_bits(m["get_from_shop"]) << np.uint32(7))
+    h = np.stack([o.hidden(i) for i in range(n)]).astype(np.uint32).view(np.int32).astype(np.int64)
+    r["turn_counter"] = h[:, 1]
+    for p in range(min(n_players, 4)):
+        r["loc"][:, p, 0] = (h[:, 4 + 2 * p] - h[:, 12]) // 2 + 1
+        r["loc"][:, p, 1] = (h[:, 5 + 2 * p] - h[:, 13]) // 2 + 1
+    return r
+
+
+def compact_mismatch(got, want):
+    a = np.ascontiguousarray(got).view(np.uint8).reshape(-1, layout.compact_dtype.itemsize)
+    b = np.ascontiguousarray(want).view(np.uint8).reshape(-1, layout.compact_dtype.itemsize)
+    if np.array_equal(a, b):
+        return None
+    bad = np.argwhere(a != b)
+    return "record %d byte %d: %d != %d (%d bytes differ)" % (bad[0][0], bad[0][1], a[tuple(bad[0])],
+                                                               b[tuple(bad[0])], len(bad))
+
+
+def run_rollout_parity(library, oracle_cls, n, seed, difficulty, max_steps, chunks, n_slots, merged,
+                       n_players=4):
+    """The rollout ring (cog_vec_rollout_attach + fused launches) and cog_vec_compact_obs
+    against records restated from the oracle stepped one call at a time; also the one-byte
+    hex grid (BUF_GRID) against the reference-layout map observation."""
+    o = oracle_cls(n, seed)
+    c = Candidate(library, n, seed)
+    try:
+        o.reset(seed, n_players, 3, difficulty, max_steps)
+        c.reset(seed, n_players, 3, difficulty, max_steps)
+        c.vec.rollout_attach(n_slots)
+        want = np.zeros((n_slots, n), dtype=layout.compact_dtype)
+        t = 0
+        dones = wins = 0
+        for k in chunks:
+            for _ in range(k):
+                r = compact_expected(o, merged, n_players)
+                if merged:
+                    o.sample(merged_masks(oracle_snapshot(o)))
+                else:
+                    o.sample()
+                r["action"] = pb(o.actions)
+                o.step()
+                r["done"] = o.dones
+                r["filled"] = 1
+                r["rewards"] = np.where(o.dones[:, None], o.rewards, 0)
+                r["t"] = t
+                want[t % n_slots] = r
+                t += 1
+                dones += int(o.dones.sum())
+                wins += int((r["rewards"] != 0).any(axis=1).sum())
+            c.vec.run_fused(c.smp, k, merged=merged)
+            bad = first_mismatch(c.snapshot(), oracle_snapshot(o))
+            assert bad is None, bad
+            _, slots, recorded = c.vec.rollout_info()
+            assert slots == n_slots and recorded == t
+            bad = compact_mismatch(c.vec.read_rollout(), want)
+            assert bad is None, "ring after %d steps: %s" % (t, bad)
+            bad = compact_mismatch(c.vec.compact_obs(merged=merged), compact_expected(o, merged, n_players))
+            assert bad is None, "compact_obs after %d steps: %s" % (t, bad)
+            grid = c.vec.read(layout.BUF_GRID)
+            assert np.array_equal(layout.grid_to_map(grid), o.observations["shared"]["map"]), "hex grid"
+        c.vec.rollout_attach(0)
+        assert c.vec.rollout_info() == (None, 0, 0)
+        return dones, wins
+    finally:
+        c.close()
+        o.close()

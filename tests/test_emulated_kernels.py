@@ -57,3 +57,17 @@ def test_emulated_fused_merged_masks(emu, oracle_cls):
 
 def test_emulated_host_io(emu, oracle_cls):
     assert parity.run_host_io_parity(emu, oracle_cls, 10, 5, layout.HARD, 6, 120) > 0
+
+
+@pytest.mark.parametrize("merged,difficulty,max_steps,n_players,chunks,n_slots", [
+    (False, layout.HARD, 8, 4, [5, 40, 33], 64),      # episode ends inside launches: tail kernel fills rewards
+    (True, layout.EASY, 100000, 4, [30, 500, 300], 1024),  # moves, purchases, a win (non-zero rewards)
+    (True, layout.HARD, 12, 3, [25, 48], 16),          # ring wraps, also within one launch
+])
+def test_emulated_rollout_and_compact_obs(emu, oracle_cls, merged, difficulty, max_steps, n_players, chunks, n_slots):
+    # compact records in the rollout ring and from cog_vec_compact_obs
+    dones, wins = parity.run_rollout_parity(emu, oracle_cls, 12, 4711, difficulty, max_steps, chunks, n_slots,
+                                            merged, n_players=n_players)
+    assert dones > 0
+    if max_steps > 100:
+        assert wins > 0

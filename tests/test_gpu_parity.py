@@ -148,3 +148,21 @@ def test_host_io_pipeline(cuda_lib, oracle_cls, n, regime):
     """sample / step through HOST buffers with chunked copy/compute overlap (several chunks,
     a ragged last one) == the oracle at every step."""
     assert parity.run_host_io_parity(cuda_lib, oracle_cls, n, 99, layout.HARD, 10, 150, regime) > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,merged,difficulty,max_steps,n_players,chunks,n_slots", [
+    (6000, False, layout.HARD, 8, 4, (3, 30, 20), 32),      # several envs per warp, ring wraps, tail kernel
+    (3000, True, layout.EASY, 60, 4, (40, 60), 128),        # moves, purchases, removals
+    (64, True, layout.EASY, 100000, 4, (900, 600), 2048),   # wins: non-zero rewards in the ring
+    (500, True, layout.HARD, 12, 2, (25, 48), 16),
+])
+def test_rollout_ring_and_compact_obs(cuda_lib, oracle_cls, n, merged, difficulty, max_steps, n_players, chunks,
+                                      n_slots):
+    """the rollout ring written by the fused kernels, cog_vec_compact_obs
+    and the one-byte hex grid == records restated from the oracle, byte for byte."""
+    dones, wins = parity.run_rollout_parity(cuda_lib, oracle_cls, n, 4711, difficulty, max_steps, chunks, n_slots,
+                                            merged, n_players=n_players)
+    assert dones > 0
+    if max_steps > 100:
+        assert wins > 0

@@ -94,6 +94,31 @@ def _check_api(cog, oracle_cls, steps, n):
     r.sync()
     assert np.array_equal(pb(envs.observations.numpy()), pb(o.observations))
     assert np.array_equal(envs.rewards.numpy(), o.rewards)
+    # compact observation, one-byte hex grid and the rollout ring (not in the reference)
+    assert np.array_equal(layout.grid_to_map(envs.hex_grid.numpy()), o.observations["shared"]["map"])
+    for merged in (True, False):
+        rec = envs.compact_observations(merged_masks=merged)
+        assert rec.numpy().dtype == layout.compact_dtype
+        assert parity.compact_mismatch(rec.numpy(), parity.compact_expected(o, merged)) is None
+    envs.attach_rollout(8)
+    want = np.zeros((8, n), dtype=layout.compact_dtype)
+    for t in range(13):
+        rec = parity.compact_expected(o, True)
+        o.sample(parity.merged_masks(parity.oracle_snapshot(o)))
+        rec["action"] = pb(o.actions)
+        o.step()
+        rec["done"], rec["filled"], rec["t"] = o.dones, 1, t
+        rec["rewards"] = np.where(o.dones[:, None], o.rewards, 0)
+        want[t % 8] = rec
+    r.run(13, merged_masks=True)
+    assert envs.rollout_steps == 13
+    ring = envs.rollout
+    assert ring.numpy().shape == (8, n) and parity.compact_mismatch(ring.numpy(), want) is None
+    if cog.__name__.endswith("_emu"):  # host pointers: numpy can consume the capsule
+        assert np.from_dlpack(ring).shape == (8, n, 256)
+    envs.attach_rollout(0)
+    with pytest.raises(ValueError):
+        envs.rollout
     with pytest.raises(RuntimeError):
         envs.reset(123, 3, 4, cog.Difficulty.EASY, 100, False)  # generate_map_failure
     with pytest.raises(ValueError):
