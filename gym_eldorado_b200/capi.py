@@ -184,9 +184,9 @@ class VecHandle:
         return p.value, t.value, c.value
 
     def read_rollout(self):
-        """The whole ring as a host array [n_slots][n] of compact records."""
+        """The whole ring as a host array [n][n_slots] of compact records (env-major)."""
         _, t, _ = self.rollout_info()
-        out = np.empty((t, self.n), dtype=layout.compact_dtype)
+        out = np.empty((self.n, t), dtype=layout.compact_dtype)
         check(self.L, self.L.cog_vec_read(self._h, layout.BUF_ROLLOUT, out.ctypes.data, out.nbytes))
         return out
 

@@ -76,7 +76,7 @@ struct cog_vec {
   void *act_staging = nullptr; /* device copy of host actions for cog_vec_step_host */
   void *merged = nullptr;      /* COG_BUF_MERGED_MASKS, allocated on first use */
   void *compact = nullptr;     /* COG_BUF_COMPACT, allocated on first use */
-  uint8_t *ring = nullptr;     /* rollout ring [ring_slots][n] compact records (cog_vec_rollout_attach) */
+  uint8_t *ring = nullptr;     /* rollout ring [n][ring_slots] compact records (cog_vec_rollout_attach) */
   uint32_t ring_slots = 0;
   uint64_t ring_steps = 0;     /* env-steps per env recorded since attach; next slot = ring_steps % ring_slots */
   cudaStream_t io[2] = {nullptr, nullptr}; /* copy/compute pipeline of the *_host_io entry points */
@@ -178,6 +178,15 @@ template <bool MERGED, bool ROLLOUT>
 void launch_fused(cog_vec *h, cog_sampler *s, unsigned grid, unsigned tail_grid, uint32_t k_steps, const cog::Rollout &R) {
   auto hot = cog::k_step_fused<MERGED, ROLLOUT>;
   auto tail = cog::k_step_tail<MERGED, ROLLOUT>;
+#ifndef COG_EMU
+  if (ROLLOUT) { /* the ring-writing kernels have their own launch bounds: fill every SM exactly once */
+    static int per_sm = 0;
+    if (!per_sm && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hot, cog::BLOCK_THREADS, 0) != cudaSuccess)
+      per_sm = 0;
+    const unsigned full = blocks_for(h->n), resident = (unsigned)(h->sm_count * (per_sm > 0 ? per_sm : 1));
+    grid = full < resident ? full : resident;
+  }
+#endif
   COG_LAUNCH(hot, grid, cog::BLOCK_THREADS, 0, h->stream, h->B, h->prm, h->n, s->srng, s->actions, k_steps, R);
   COG_LAUNCH(tail, tail_grid, cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm, h->n, s->srng,
              s->actions, k_steps, R);
@@ -537,6 +546,7 @@ int cog_vec_rollout_attach(cog_vec *h, uint32_t n_slots) {
   h->ring_slots = 0;
   h->ring_steps = 0;
   if (!n_slots) return COG_OK; /* detached */
+  if ((uint64_t)n_slots * h->n > 0xffffffffull) return fail(COG_ERR_INVALID, "rollout ring: n_envs * n_slots must fit 32 bits");
   const size_t bytes = (size_t)n_slots * h->n * COG_COMPACT_SIZE;
   cudaError_t e = cudaMalloc((void **)&h->ring, bytes);
   if (e != cudaSuccess) {
@@ -585,7 +595,6 @@ int cog_vec_run_fused_ex(cog_vec *h, cog_sampler *s, uint64_t k_steps, int mask_
   cog::Rollout R{};
   if (h->ring) {
     R.ring = h->ring;
-    R.n = h->n;
     R.T = h->ring_slots;
     R.slot0 = (uint32_t)(h->ring_steps % h->ring_slots);
     R.t0 = (uint32_t)h->ring_steps;

@@ -471,53 +471,47 @@ __device__ __forceinline__ void export_dynamic(const Env &E, const Buffers &B, u
 
 /* ---------------------------------------------------------- compact records */
 /* ring of compact records (layout: cog_layout.h) that a fused launch appends to, one record
- * per env-step: step t of env i lives at ring + ((t % T) * n + i) * COGL_CR_SIZE */
+ * per env-step, env-major: step t of env i lives at ring + (i * T + t % T) * COGL_CR_SIZE, so a
+ * warp streams its env's trajectory into consecutive 256-byte records */
 struct Rollout {
   u8 *ring;
-  u64 n;     /* envs per slot */
-  u32 T;     /* slots */
+  u32 T;     /* slots per env */
   u32 slot0; /* slot of the launch's first step */
   u32 t0;    /* index of that step since the ring was attached */
 };
 
-/* cells 0..27: the state the current agent acts from, the mask heads its action is sampled
- * from and the action itself.  Lane c assembles cell c; one 8-byte store per lane. */
+/* The part of a record that is known BEFORE the step: the state the current agent acts from,
+ * the mask heads its action is sampled from and the action.  No lane ever selects between
+ * values: the warp-uniform words leave as 16-byte stores of lane 0 alone, the per-lane data
+ * (cards: lanes 1..21, positions: lanes 0..3) as one store each under its own lane predicate. */
 __device__ __forceinline__ void compact_store_pre(u8 *rec, const Env &E, const Params &prm, u32 play, u32 spec,
-                                                  u32 rem, u32 ms, u32 act, u32 a_shop, int lane) {
-  const int np = (int)prm.n_players < 4 ? (int)prm.n_players : 4;
-  u32 g = 0; /* the cell of the hex grid the player stands on (Map::get_from_array indexing) */
-  if (lane < np)
-    g = (u32)((loc_x(E.ploc) - E.minx) / 2 + 1) | ((u32)((loc_y(E.ploc) - E.miny) / 2 + 1) << 8);
-  const u32 g01 = bcast(g, 0) | (bcast(g, 1) << 16), g23 = bcast(g, 2) | (bcast(g, 3) << 16);
-  uint2 c = make_uint2(0u, 0u);
-  if (lane >= 1 && lane <= 21) {
-    c.x = (E.draw & 0xffu) | ((E.hand & 0xffu) << 8) | ((E.active & 0xffu) << 16) | (E.played << 24);
-    c.y = (E.discard & 0xffu) | (lane <= 18 ? (E.shop & 0xffu) << 8 : 0u);
-  } else {
-    switch (lane) {
-    case 0:
-      c.x = E.agent | (E.phase << 8) | (((u32)E.res[0] & 0xffffu) << 16);
-      c.y = ((u32)E.res[1] & 0xffffu) | (((u32)E.res[2] & 0xffffu) << 16);
-      break;
-    case 22: c.x = act; c.y = a_shop; break;
-    case 23: c.x = play; c.y = rem; break;
-    case 24: c.x = ms; c.y = spec; break;
-    case 25: c.x = g01; c.y = g23; break;
-    case 26: c.x = E.turn; break;
-    default: break;
-    }
-  }
-  if (lane < COGL_CR_PRE_CELLS) reinterpret_cast<uint2 *>(rec)[lane] = c;
+                                                  u32 rem, u32 ms, u32 act, u32 a_shop, u32 t, int lane) {
+  const u32 hx = __byte_perm(E.agent | (E.phase << 8), (u32)E.res[0], 0x5410);
+  const u32 hy = __byte_perm((u32)E.res[1], (u32)E.res[2], 0x5410);
+  if (lane == 0) *reinterpret_cast<uint4 *>(rec + COGL_CR_HEAD) = make_uint4(hx, hy, act, a_shop);
+  if (lane == 0) *reinterpret_cast<uint4 *>(rec + COGL_CR_MASK_PLAY) = make_uint4(play, rem, ms, spec);
+  if (lane == 0) *reinterpret_cast<uint2 *>(rec + COGL_CR_TURN) = make_uint2(E.turn, t);
+  /* the cell of the hex grid a player stands on (Map::get_from_array indexing).  A player's
+   * hex is never left of / below the board's minimum and both differences are even, so the
+   * two 16-bit halves of the packed location subtract (offset-binary: no borrow between the
+   * halves), halve and increment as one word. */
+  const u32 mn = __byte_perm((u32)E.minx, (u32)E.miny, 0x5410);
+  const u32 h = (((E.ploc ^ 0x80008000u) - (mn ^ 0x80008000u)) >> 1) + 0x00010001u;
+  const u32 g = __byte_perm(h, 0u, 0x4420); /* row | col << 8 */
+  if (lane < 4)
+    reinterpret_cast<unsigned short *>(rec + COGL_CR_LOC)[lane] = (unsigned short)(lane < (int)prm.n_players ? g : 0u);
+  /* byte 0 (the current agent) of the five pile words and of the shop word (zero in the lanes
+   * that are no shop slot): three PRMT for the low word, one PRMT + mask for the high */
+  const u32 x = __byte_perm(__byte_perm(E.draw, E.hand, 0x0040), __byte_perm(E.active, E.played, 0x0040), 0x5410);
+  const u32 y = __byte_perm(E.discard, E.shop, 0x0040) & 0xffffu;
+  if ((unsigned)(lane - 1) < 21u) reinterpret_cast<uint2 *>(rec + COGL_CR_CARDS - 8)[lane] = make_uint2(x, y);
 }
-/* cells 28..31 (one 32-byte sector): the outcome of the step taken from that state */
-__device__ __forceinline__ void compact_store_post(u8 *rec, u32 done, u32 filled, u32 r01lo, u32 r01hi, u32 r23lo,
-                                                   u32 r23hi, u32 t, int lane) {
-  uint2 c = make_uint2(0u, 0u);
-  if (lane == 28) c.x = done | (filled << 8);
-  if (lane == 29) { c.x = r01lo; c.y = r01hi; }
-  if (lane == 30) { c.x = r23lo; c.y = r23hi; }
-  if (lane == 31) c.x = t;
-  if (lane >= COGL_CR_PRE_CELLS) reinterpret_cast<uint2 *>(rec)[lane] = c;
+/* the outcome of the step taken from that state: done (+ "filled"), rewards zero — the
+ * kernel that finishes an episode overwrites them (compact_store_rewards) */
+__device__ __forceinline__ void compact_store_post(u8 *rec, u32 done, u32 filled, int lane) {
+  if (lane < 2)
+    *reinterpret_cast<uint4 *>(rec + COGL_CR_DONE + 16 * lane) =
+        make_uint4(lane == 0 ? done | (filled << 8) : 0u, 0u, 0u, 0u);
 }
 /* the rewards of an episode end (get_reward src/environment.cpp:281-288) into the record of
  * the step that ended it.  Call after env_finish_episode (absolute player order). */
@@ -525,11 +519,10 @@ __device__ __forceinline__ void compact_store_rewards(u8 *rec, const Env &E, con
   const int np = (int)prm.n_players < 4 ? (int)prm.n_players : 4;
   const bool won = lane < 4 && (E.pf & PFL_WON);
   const int n_winners = __popc(__ballot_sync(COG_FULL, won));
-  u32 r = 0;
-  if (lane < np) r = __float_as_uint((float)((int)prm.n_players * (won ? 1 : 0) - n_winners));
-  const u32 r0 = bcast(r, 0), r1 = bcast(r, 1), r2 = bcast(r, 2), r3 = bcast(r, 3);
-  if (lane == 29) *reinterpret_cast<uint2 *>(rec + COGL_CR_REWARDS) = make_uint2(r0, r1);
-  if (lane == 30) *reinterpret_cast<uint2 *>(rec + COGL_CR_REWARDS + 8) = make_uint2(r2, r3);
+  __syncwarp(); /* lane 1 zeroed these words in compact_store_post */
+  if (lane < 4)
+    reinterpret_cast<float *>(rec + COGL_CR_REWARDS)[lane] =
+        lane < np ? (float)((int)prm.n_players * (won ? 1 : 0) - n_winners) : 0.0f;
 }
 
 /* ------------------------------------------------------------------- decks */

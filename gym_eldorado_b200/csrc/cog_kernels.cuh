@@ -111,6 +111,15 @@ __device__ __forceinline__ void store_action(u8 *actions_out, u64 i, u32 act, u3
 #ifndef COG_TAIL_BLOCKS
 #define COG_TAIL_BLOCKS 8 /* board generation is latency-bound: occupancy beats spills */
 #endif
+/* resident blocks per SM of the fused kernels that also write the rollout ring: the record
+ * assembly wants registers more than a ninth block (measured: 7 blocks 3.31e9, 8 3.17e9, 9 2.97e9
+ * env-steps/s sampling from selected_action_masks; 1.90 / 1.95 / 1.86e9 from merged masks) */
+#ifndef COG_RING_BLOCKS
+#define COG_RING_BLOCKS 7
+#endif
+#ifndef COG_RING_BLOCKS_MERGED
+#define COG_RING_BLOCKS_MERGED 8
+#endif
 #ifndef COG_MIN_BLOCKS
 #define COG_MIN_BLOCKS 9
 #endif
@@ -128,24 +137,26 @@ __device__ __forceinline__ u32 sample_and_step(Env &E, u32 &sr, u32 &act, u32 &a
     u32 rem, ms;
     merged_heads(E, lane, rem, ms);
     sample_action(sr, E.Splay, spec_of(E.Splay), rem, ms, act, a_shop, lane);
-    if (ROLLOUT) compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), rem, ms, act, a_shop, lane);
+    if (ROLLOUT) compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), rem, ms, act, a_shop, t, lane);
     status = env_step<false, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
   } else {
     const bool play_only = sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane);
-    if (ROLLOUT) compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane);
+    if (ROLLOUT) compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, t, lane);
     if (play_only) status = env_step<true, true>(E, act, 0, prm, B, i, obs_pending, lane);
     else status = env_step<true, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
   }
   /* rewards stay zero here: the kernel that finishes the episode fills them in */
-  if (ROLLOUT) compact_store_post(rec, status & 1u, 1u, 0u, 0u, 0u, 0u, t, lane);
+  if (ROLLOUT) compact_store_post(rec, status & 1u, 1u, lane);
   return status;
 }
-__device__ __forceinline__ u8 *rollout_rec(const Rollout &R, u32 slot, u64 i) {
-  return R.ring + ((u64)slot * R.n + i) * COGL_CR_SIZE;
+/* the record of slot `slot` of env i.  A 32-bit record index (the host checks n * T < 2^32)
+ * keeps this at two instructions wherever the compiler chooses to recompute it. */
+__device__ __forceinline__ u8 *rollout_rec(const Rollout &R, u32 i, u32 slot) {
+  return R.ring + (u64)(i * R.T + slot) * COGL_CR_SIZE;
 }
 
 template <bool MERGED, bool ROLLOUT>
-__global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step_fused(Buffers B, Params prm, u64 n, u32 *srng,
+__global__ void __launch_bounds__(BLOCK_THREADS, ROLLOUT ? (MERGED ? COG_RING_BLOCKS_MERGED : COG_RING_BLOCKS) : COG_MIN_BLOCKS) k_step_fused(Buffers B, Params prm, u64 n, u32 *srng,
                                                                              u8 *actions_out, u32 k_steps, Rollout R) {
   const int lane = threadIdx.x & 31;
 #ifdef COG_UNIFORM_PROOF
@@ -173,7 +184,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_MIN_BLOCKS) k_step_fused(Bu
     u32 slot = R.slot0, t = R.t0;
     do {
       status = sample_and_step<MERGED, ROLLOUT>(E, sr, act, a_shop, prm, B, i, obs_pending,
-                                                ROLLOUT ? rollout_rec(R, slot, i) : nullptr, t, lane);
+                                                ROLLOUT ? rollout_rec(R, (u32)i, slot) : nullptr, t, lane);
       if (ROLLOUT) {
         ++t;
         if (++slot == R.T) slot = 0;
@@ -229,7 +240,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Bu
       const u32 j_done = k_steps - parked;
       slot = (u32)(((u64)R.slot0 + j_done) % R.T);
       t = R.t0 + j_done;
-      rec = rollout_rec(R, slot, i);
+      rec = rollout_rec(R, (u32)i, slot);
     }
     for (u32 j = 0;; ++j) {
       if (status & 1u) { /* rewards / Info / aggregates, then auto-reset: the RNG stream continues */
@@ -241,7 +252,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Bu
       if (ROLLOUT) {
         ++t;
         if (++slot == R.T) slot = 0;
-        rec = rollout_rec(R, slot, i);
+        rec = rollout_rec(R, (u32)i, slot);
       }
       status = sample_and_step<MERGED, ROLLOUT>(E, sr, act, a_shop, prm, B, i, obs_pending, rec, t, lane);
     }
@@ -284,8 +295,9 @@ __global__ void k_compact_obs(Buffers B, Params prm, u64 n, u8 *out, int merged)
   u32 rem = E.Srem, ms = E.Sms;
   if (merged) merged_heads(E, lane, rem, ms);
   u8 *rec = out + i * COGL_CR_SIZE;
-  compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), rem, ms, 0u, 0u, lane);
-  compact_store_post(rec, 0u, 0u, 0u, 0u, 0u, 0u, 0u, lane);
+  reinterpret_cast<uint2 *>(rec)[lane] = make_uint2(0u, 0u); /* caller memory: padding included */
+  __syncwarp();
+  compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), rem, ms, 0u, 0u, 0u, lane);
 }
 
 /* vec_action_sampler<N>::sample include/vec_sampler.h:14-21 on ActionMask[n] records:

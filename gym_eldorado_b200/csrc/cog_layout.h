@@ -77,35 +77,32 @@ enum {
 
 /* ------------------------------------------------------------------------------------------
  * Compact record (not in the reference): one env as seen by its current
- * agent in 256 bytes = 32 cells of 8 bytes, cell c written by lane c in ONE coalesced store.
- * It carries every dynamic field of ObsData that the acting agent needs (the 48x48x7 map is
- * static per episode and lives in COG_BUF_GRID, one byte per hex) plus the players' grid
- * positions, which the reference never exports (map feature 0 is never written, SURVEY A#1).
+ * agent in 256 bytes.  It carries every dynamic field of ObsData that the acting agent needs
+ * (the 48x48x7 map is static per episode and lives in COG_BUF_GRID, one byte per hex) plus the
+ * players' grid positions, which the reference never exports (map feature 0 is never written,
+ * SURVEY A#1).  The layout follows the warp that writes it: warp-uniform words sit in 16-byte
+ * units that lane 0 stores whole, per-lane data where its lane stores it.
  *
- *  cell 0       b0 agent_selection, b1 phase, u16 current_resources[k] * 2 at b2, b4, b6
- *  cell 1..21   card type c = cell - 1 of the CURRENT agent: b0 draw, b1 hand, b2 active,
- *               b3 played, b4 discard, b5 shop stock of slot c (cells 1..18, else 0), b6-7 zero
- *  cell 22      the action taken from this state: b0 play, b1 play_special, b2 remove, b3 move,
- *               b4 get_from_shop (zero in cog_vec_compact_obs)
- *  cell 23      u32 mask.play bits 0-21, u32 mask.remove bits 0-21
- *  cell 24      u32 mask.move bits 0-6 | mask.get_from_shop << 7, u32 mask.play_special
- *  cell 25      b(2p) / b(2p+1) = grid row / column of player p (the cell of COG_BUF_GRID
- *               it stands on); zero for p >= n_players
- *  cell 26      u32 turn_counter, u32 zero
- *  cell 27      zero
- *  cell 28      b0 done (the step taken from this state ended the episode), b1 = 1 when cells
- *               22 and 28-31 are filled in (rollout records), rest zero
- *  cell 29-30   float rewards[4] of that step (the env's rewards when done, else 0)
- *  cell 31      u32 index of the step since cog_vec_rollout_attach, u32 zero
+ *    0  u8 agent_selection, u8 phase, u16 current_resources[3] * 2
+ *    8  the action taken from this state: u8 play, play_special, remove, move, get_from_shop,
+ *       3 zero bytes (all zero in cog_vec_compact_obs)
+ *   16  u32 mask.play (bit k = play[k]), u32 mask.remove,
+ *       u32 mask.move (bits 0-6) | mask.get_from_shop << 7 (bits 7-25), u32 mask.play_special
+ *   32  4 x { u8 row, u8 col }: the cell of COG_BUF_GRID player p stands on (0, 0 for p >= n_players)
+ *   40  u32 turn_counter, u32 index of the step since cog_vec_rollout_attach (low 32 bits)
+ *   48  u8 done (the step taken from this state ended the episode), u8 filled (1 in rollout
+ *       records: action, done, rewards, step index are valid), 14 zero bytes
+ *   64  float rewards[4] of that step (the env's rewards when done, else 0)
+ *   80  21 x { u8 draw, hand, active, played, discard (DeckObs of the CURRENT agent, card type c),
+ *       u8 shop stock of slot c (c < 18, else 0), 2 zero bytes }
+ *  248  8 zero bytes
  * The masks are the heads the action was (or will be) sampled from: selected_action_masks in
  * COG_MASKS_SELECTED mode, the merged legal mask in COG_MASKS_MERGED mode. */
 enum {
   COGL_CR_SIZE = 256,
-  COGL_CR_HEAD = 0, COGL_CR_CARDS = 8, COGL_CR_ACTION = 176, COGL_CR_MASK_PLAY = 184,
-  COGL_CR_MASK_REMOVE = 188, COGL_CR_MASK_MOVESHOP = 192, COGL_CR_MASK_SPECIAL = 196,
-  COGL_CR_LOC = 200, COGL_CR_TURN = 208, COGL_CR_DONE = 224, COGL_CR_REWARDS = 232,
-  COGL_CR_T = 248,
-  COGL_CR_PRE_CELLS = 28 /* cells 0..27 describe the state, 28..31 the outcome of the step */
+  COGL_CR_HEAD = 0, COGL_CR_ACTION = 8, COGL_CR_MASK_PLAY = 16, COGL_CR_MASK_REMOVE = 20,
+  COGL_CR_MASK_MOVESHOP = 24, COGL_CR_MASK_SPECIAL = 28, COGL_CR_LOC = 32, COGL_CR_TURN = 40, COGL_CR_T = 44,
+  COGL_CR_DONE = 48, COGL_CR_REWARDS = 64, COGL_CR_CARDS = 80
 };
 
 #endif

@@ -215,8 +215,8 @@ public:
       b.np_dtype = py::dtype("bool"); b.typestr = "|b1"; b.shape = {(int64_t)n}; b.dl = {kDLBool, 8, 1};
     } else if (which == COG_BUF_AGENT_SELECTION) {
       b.np_dtype = py::dtype("uint8"); b.typestr = "|u1"; b.shape = {(int64_t)n}; b.dl = {kDLUInt, 8, 1};
-    } else if (which == COG_BUF_ROLLOUT) { /* time-major [n_slots][n] records */
-      b.typestr = "|u1"; b.shape = {(int64_t)(b.count / n), (int64_t)n, (int64_t)b.itemsize}; b.dl = {kDLUInt, 8, 1};
+    } else if (which == COG_BUF_ROLLOUT) { /* env-major [n][n_slots] records */
+      b.typestr = "|u1"; b.shape = {(int64_t)n, (int64_t)(b.count / n), (int64_t)b.itemsize}; b.dl = {kDLUInt, 8, 1};
     } else {
       b.typestr = "|u1"; b.shape = {(int64_t)n, (int64_t)b.itemsize}; b.dl = {kDLUInt, 8, 1};
     }
@@ -382,7 +382,8 @@ PYBIND11_MODULE(COG_MODULE_NAME, m) {
       .def("attach_rollout", [](VecEnv &e, uint32_t n_slots) { ck(cog_vec_rollout_attach(e.own->h, n_slots)); },
            py::arg("n_slots"),
            "not in the reference: every later runner.run() appends one compact record per env-step (state, "
-           "mask sampled from, action, done, rewards) to a device ring [n_slots][n]; 0 detaches")
+           "mask sampled from, action, done, rewards) to a device ring [n][n_slots] (each env's trajectory is "
+           "contiguous); 0 detaches")
       .def_property_readonly("rollout", [](const VecEnv &e) { return e.view(COG_BUF_ROLLOUT); })
       .def_property_readonly("rollout_steps",
                              [](const VecEnv &e) {

@@ -95,13 +95,16 @@ compact_card_dtype = np.dtype({
     "offsets": [0, 1, 2, 3, 4, 5],
     "itemsize": 8,
 })
+compact_loc_dtype = np.dtype({"names": ["row", "col"], "formats": [np.uint8, np.uint8], "offsets": [0, 1],
+                              "itemsize": 2})
 compact_dtype = np.dtype({
-    "names": ["agent_selection", "phase", "resources_x2", "cards", "action", "mask_play", "mask_remove",
-              "mask_move_shop", "mask_play_special", "loc", "turn_counter", "done", "filled", "rewards", "t"],
-    "formats": [np.uint8, np.uint8, (np.uint16, (N_RESOURCETYPES,)), (compact_card_dtype, (N_CARDTYPES,)),
-                (np.uint8, (5,)), np.uint32, np.uint32, np.uint32, np.uint32, (np.uint8, (MAX_N_PLAYERS, 2)),
-                np.uint32, np.uint8, np.uint8, (np.float32, (MAX_N_PLAYERS,)), np.uint32],
-    "offsets": [0, 1, 2, 8, 176, 184, 188, 192, 196, 200, 208, 224, 225, 232, 248],
+    "names": ["agent_selection", "phase", "resources_x2", "action", "mask_play", "mask_remove",
+              "mask_move_shop", "mask_play_special", "loc", "turn_counter", "t", "done", "filled", "rewards",
+              "cards"],
+    "formats": [np.uint8, np.uint8, (np.uint16, (N_RESOURCETYPES,)), (np.uint8, (5,)), np.uint32, np.uint32,
+                np.uint32, np.uint32, (compact_loc_dtype, (MAX_N_PLAYERS,)), np.uint32, np.uint32, np.uint8,
+                np.uint8, (np.float32, (MAX_N_PLAYERS,)), (compact_card_dtype, (N_CARDTYPES,))],
+    "offsets": [0, 1, 2, 8, 16, 20, 24, 28, 32, 40, 44, 48, 49, 64, 80],
     "itemsize": 256,
 })
 GRID_BYTES = GRIDSIZE * GRIDSIZE

@@ -71,8 +71,8 @@ typedef enum cog_buffer {
                                   Constant within an episode; rewritten by every (auto-)reset */
   COG_BUF_COMPACT = 8,         /* not in the reference: one 256-byte compact record per env (below);
                                   allocated on first use, refreshed by cog_vec_compact_obs(h, NULL, mode) */
-  COG_BUF_ROLLOUT = 9          /* not in the reference: the rollout ring, n_slots * n compact records
-                                  (count = n_slots * n); only after cog_vec_rollout_attach */
+  COG_BUF_ROLLOUT = 9          /* not in the reference: the rollout ring, [n][n_slots] compact records
+                                  (count = n * n_slots); only after cog_vec_rollout_attach */
 } cog_buffer;
 #define COG_GRID_BYTES 2304
 #define COG_COMPACT_SIZE 256
@@ -181,22 +181,21 @@ COG_API int cog_vec_merged_masks(cog_vec *h, void *d_out);
 /* Compact observation.  The reference's ObsData is 17216 B per env, 94 % of it
  * the 48x48x7 map that never changes within an episode (and whose "occupying player" feature
  * is never written).  The compact record carries what the CURRENT agent acts
- * on in 256 bytes = 32 cells of 8 bytes; together with COG_BUF_GRID it restates every field
- * of ObsData the agent can use, plus the players' positions:
- *   cell 0      b0 agent_selection, b1 phase, u16 current_resources[k] * 2 at bytes 2, 4, 6
- *   cell 1..21  card type c = cell - 1 of the current agent: b0 draw, b1 hand, b2 active,
- *               b3 played, b4 discard (DeckObs, include/api.h:67-81), b5 shop stock of slot c
- *               (cells 1..18), b6-7 zero
- *   cell 22     ActionData taken from this state: play, play_special, remove, move,
- *               get_from_shop, 3 zero bytes (all zero in cog_vec_compact_obs)
- *   cell 23     u32 mask.play (bit k = play[k]), u32 mask.remove
- *   cell 24     u32 mask.move (bits 0-6) | mask.get_from_shop << 7 (bits 7-25), u32 mask.play_special
- *   cell 25     b(2p), b(2p+1) = row, column in COG_BUF_GRID of the hex player p stands on
- *               (zero for p >= n_players)
- *   cell 26     u32 turn_counter, u32 zero          cell 27  zero
- *   cell 28     b0 done, b1 = 1 if cells 22 and 28-31 are filled in (rollout records), rest zero
- *   cell 29-30  float rewards[4] (the env's rewards when that step ended the episode, else 0)
- *   cell 31     u32 step index since cog_vec_rollout_attach (low 32 bits), u32 zero
+ * on in 256 bytes; together with COG_BUF_GRID it restates every field of ObsData the agent
+ * can use, plus the players' positions (byte offsets):
+ *     0  u8 agent_selection, u8 phase, u16 current_resources[3] * 2
+ *     8  ActionData taken from this state: u8 play, play_special, remove, move, get_from_shop,
+ *        3 zero bytes (all zero in cog_vec_compact_obs)
+ *    16  u32 mask.play (bit k = play[k]), u32 mask.remove,
+ *        u32 mask.move (bits 0-6) | mask.get_from_shop << 7 (bits 7-25), u32 mask.play_special
+ *    32  4 x { u8 row, u8 col }: the cell of COG_BUF_GRID player p stands on (0, 0 for p >= n_players)
+ *    40  u32 turn_counter, u32 step index since cog_vec_rollout_attach (low 32 bits)
+ *    48  u8 done, u8 filled (1 in rollout records: action, done, rewards, step index are valid),
+ *        14 zero bytes
+ *    64  float rewards[4] (the env's rewards when that step ended the episode, else 0)
+ *    80  21 x { u8 draw, hand, active, played, discard of card type c in the current agent's
+ *        DeckObs (include/api.h:67-81), u8 shop stock of slot c (c < 18, else 0), 2 zero bytes }
+ *   248  8 zero bytes
  * The mask words are selected_action_masks (COG_MASKS_SELECTED) or the merged legal mask
  * (COG_MASKS_MERGED).  Writes n_envs records to DEVICE memory d_out, or to COG_BUF_COMPACT
  * when d_out == NULL. */
@@ -205,13 +204,14 @@ COG_API int cog_vec_compact_obs(cog_vec *h, void *d_out, int mask_mode);
 /* Rollout writer (the reference leaves this to the user: "copy the views into
  * your own buffers", docs/source/index.rst:20-26).  After cog_vec_rollout_attach(h, T) every
  * cog_vec_run_fused(_ex) launch appends one compact record per env-step to a device ring of
- * T slots: step t (counted per env since attach) of env i is at
- *   ring + ((t % T) * n_envs + i) * COG_COMPACT_SIZE
+ * T slots per env, env-major: step t (counted per env since attach) of env i is at
+ *   ring + (i * T + t % T) * COG_COMPACT_SIZE
  * holding the state BEFORE the step, the mask heads the action was sampled from, the action,
- * and done / rewards AFTER it — what a PPO-style trainer consumes, [T][n_envs] time-major.
- * The ring costs T * n_envs * 256 bytes; n_slots == 0 detaches and frees it.
- * cog_vec_rollout_info returns the ring, its size and the number of steps recorded so far
- * (the next record goes to slot steps % T). */
+ * and done / rewards AFTER it — what a PPO-style trainer consumes; each env's trajectory is
+ * contiguous (returns / advantages scan along it), and the warp that owns the env streams it
+ * out as consecutive 256-byte records.  The ring costs n_envs * T * 256 bytes; n_slots == 0
+ * detaches and frees it.  cog_vec_rollout_info returns the ring, its size and the number of
+ * steps recorded so far (the next record goes to slot steps % T). */
 COG_API int cog_vec_rollout_attach(cog_vec *h, uint32_t n_slots);
 COG_API int cog_vec_rollout_info(cog_vec *h, void **d_ring, uint32_t *n_slots, uint64_t *steps_recorded);
 

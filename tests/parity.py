@@ -257,8 +257,8 @@ def compact_expected(o, merged, n_players=4):
     h = np.stack([o.hidden(i) for i in range(n)]).astype(np.uint32).view(np.int32).astype(np.int64)
     r["turn_counter"] = h[:, 1]
     for p in range(min(n_players, 4)):
-        r["loc"][:, p, 0] = (h[:, 4 + 2 * p] - h[:, 12]) // 2 + 1
-        r["loc"][:, p, 1] = (h[:, 5 + 2 * p] - h[:, 13]) // 2 + 1
+        r["loc"]["row"][:, p] = (h[:, 4 + 2 * p] - h[:, 12]) // 2 + 1
+        r["loc"]["col"][:, p] = (h[:, 5 + 2 * p] - h[:, 13]) // 2 + 1
     return r
 
 
@@ -283,7 +283,7 @@ def run_rollout_parity(library, oracle_cls, n, seed, difficulty, max_steps, chun
         o.reset(seed, n_players, 3, difficulty, max_steps)
         c.reset(seed, n_players, 3, difficulty, max_steps)
         c.vec.rollout_attach(n_slots)
-        want = np.zeros((n_slots, n), dtype=layout.compact_dtype)
+        want = np.zeros((n, n_slots), dtype=layout.compact_dtype)
         t = 0
         dones = wins = 0
         for k in chunks:
@@ -299,7 +299,7 @@ def run_rollout_parity(library, oracle_cls, n, seed, difficulty, max_steps, chun
                 r["filled"] = 1
                 r["rewards"] = np.where(o.dones[:, None], o.rewards, 0)
                 r["t"] = t
-                want[t % n_slots] = r
+                want[:, t % n_slots] = r
                 t += 1
                 dones += int(o.dones.sum())
                 wins += int((r["rewards"] != 0).any(axis=1).sum())

@@ -101,7 +101,7 @@ def _check_api(cog, oracle_cls, steps, n):
         assert rec.numpy().dtype == layout.compact_dtype
         assert parity.compact_mismatch(rec.numpy(), parity.compact_expected(o, merged)) is None
     envs.attach_rollout(8)
-    want = np.zeros((8, n), dtype=layout.compact_dtype)
+    want = np.zeros((n, 8), dtype=layout.compact_dtype)
     for t in range(13):
         rec = parity.compact_expected(o, True)
         o.sample(parity.merged_masks(parity.oracle_snapshot(o)))
@@ -109,13 +109,13 @@ def _check_api(cog, oracle_cls, steps, n):
         o.step()
         rec["done"], rec["filled"], rec["t"] = o.dones, 1, t
         rec["rewards"] = np.where(o.dones[:, None], o.rewards, 0)
-        want[t % 8] = rec
+        want[:, t % 8] = rec
     r.run(13, merged_masks=True)
     assert envs.rollout_steps == 13
     ring = envs.rollout
-    assert ring.numpy().shape == (8, n) and parity.compact_mismatch(ring.numpy(), want) is None
+    assert ring.numpy().shape == (n, 8) and parity.compact_mismatch(ring.numpy(), want) is None
     if cog.__name__.endswith("_emu"):  # host pointers: numpy can consume the capsule
-        assert np.from_dlpack(ring).shape == (8, n, 256)
+        assert np.from_dlpack(ring).shape == (n, 8, 256)
     envs.attach_rollout(0)
     with pytest.raises(ValueError):
         envs.rollout
