@@ -349,6 +349,17 @@ __device__ __forceinline__ u32 hid_word(const u32 *rec, int w) {
   return rec[w];
 }
 template <bool L2 = false>
+__device__ __forceinline__ uint4 hid_vec(const u32 *rec, int w) {
+#ifndef COG_EMU
+  if (L2) return __ldcg(reinterpret_cast<const uint4 *>(rec + w));
+#endif
+  return *reinterpret_cast<const uint4 *>(rec + w);
+}
+/* No shuffles: the seven per-lane lines are one coalesced load each; the player line and the
+ * env scalars are read as 16-byte vectors straight from the addresses every lane needs (lane l
+ * wants the fields of player l & 3 and all sixteen scalars) — same-address lanes share one
+ * transaction, so this is 6 vector loads instead of 2 loads + 27 shuffles. */
+template <bool L2 = false>
 __device__ __forceinline__ void env_load(Env &E, const u32 *rec, int lane) {
   E.lc = LANE_CONST[lane];
   E.draw = hid_word<L2>(rec, COG_HL_DRAW * 32 + lane);
@@ -358,36 +369,37 @@ __device__ __forceinline__ void env_load(Env &E, const u32 *rec, int lane) {
   E.discard = hid_word<L2>(rec, COG_HL_DISCARD * 32 + lane);
   E.shop = hid_word<L2>(rec, COG_HL_SHOP * 32 + lane);
   E.nbr = hid_word<L2>(rec, COG_HL_NBR * 32 + lane);
-  const u32 pw = hid_word<L2>(rec, COG_HL_PLAYER * 32 + lane);
-  const u32 ew = hid_word<L2>(rec, COG_HL_ENV * 32 + lane);
-  const int q = lane & 3;
-  E.pf = bcast(pw, 4 * COG_PF_FLAGS + q);
-  E.pc = bcast(pw, 4 * COG_PF_COUNTS + q);
-  E.pmv = bcast(pw, 4 * COG_PF_MOVES + q);
-  E.ploc = bcast(pw, 4 * COG_PF_LOC + q);
-  E.Pplay = bcast(pw, 4 * COG_PF_MPLAY + q);
-  E.Prem = bcast(pw, 4 * COG_PF_MREM + q);
-  E.Pms = bcast(pw, 4 * COG_PF_MMS + q);
-  E.rng = bcast(ew, COG_ES_RNG);
-  E.turn = bcast(ew, COG_ES_TURN);
-  const u32 misc = bcast(ew, COG_ES_MISC);
-  E.agent = misc & 0xffu;
-  E.phase = (misc >> 8) & 0xffu;
-  E.n_in_market = (misc >> 16) & 0xffu;
-  E.res[0] = (int)bcast(ew, COG_ES_RES0);
-  E.res[1] = (int)bcast(ew, COG_ES_RES1);
-  E.res[2] = (int)bcast(ew, COG_ES_RES2);
-  const u32 mn = bcast(ew, COG_ES_MIN);
-  E.minx = loc_x(mn);
-  E.miny = loc_y(mn);
-  E.Splay = bcast(ew, COG_ES_SPLAY);
-  E.Srem = bcast(ew, COG_ES_SREM);
-  E.Sms = bcast(ew, COG_ES_SMS);
-  E.info_steps = bcast(ew, COG_ES_INFOSTEPS);
-  E.cpf = bcast(ew, COG_ES_CPF);
-  E.cpc = bcast(ew, COG_ES_CPC);
+  const int pbase = COG_HL_PLAYER * 32 + COG_PF_STRIDE * (lane & 3);
+  const uint4 p0 = hid_vec<L2>(rec, pbase), p1 = hid_vec<L2>(rec, pbase + 4);
+  E.pf = p0.x;    /* COG_PF_FLAGS */
+  E.pc = p0.y;    /* COG_PF_COUNTS */
+  E.pmv = p0.z;   /* COG_PF_MOVES */
+  E.ploc = p0.w;  /* COG_PF_LOC */
+  E.Pplay = p1.x; /* COG_PF_MPLAY */
+  E.Prem = p1.z;  /* COG_PF_MREM */
+  E.Pms = p1.w;   /* COG_PF_MMS */
+  const uint4 e0 = hid_vec<L2>(rec, COG_HL_ENV * 32), e1 = hid_vec<L2>(rec, COG_HL_ENV * 32 + 4);
+  const uint4 e2 = hid_vec<L2>(rec, COG_HL_ENV * 32 + 8), e3 = hid_vec<L2>(rec, COG_HL_ENV * 32 + 12);
+  E.rng = e0.x;  /* COG_ES_RNG */
+  E.turn = e0.y; /* COG_ES_TURN */
+  E.agent = e0.z & 0xffu; /* COG_ES_MISC */
+  E.phase = (e0.z >> 8) & 0xffu;
+  E.n_in_market = (e0.z >> 16) & 0xffu;
+  E.res[0] = (int)e0.w; /* COG_ES_RES0.. */
+  E.res[1] = (int)e1.x;
+  E.res[2] = (int)e1.y;
+  E.minx = loc_x(e1.z); /* COG_ES_MIN */
+  E.miny = loc_y(e1.z);
+  E.Splay = e1.w; /* COG_ES_SPLAY */
+  E.Srem = e2.y;  /* COG_ES_SREM */
+  E.Sms = e2.z;   /* COG_ES_SMS */
+  E.info_steps = e2.w; /* COG_ES_INFOSTEPS */
+  E.cpf = e3.x;   /* COG_ES_CPF */
+  E.cpc = e3.y;   /* COG_ES_CPC */
 }
 
+/* the mirror image: lanes 0..3 store their player's eight words, lane 0 the sixteen scalars,
+ * as 16-byte vectors — no shuffles, no per-lane selection */
 __device__ __forceinline__ void env_store(const Env &E, u32 *rec, int lane, u32 pending = 0) {
   rec[COG_HL_DRAW * 32 + lane] = E.draw;
   rec[COG_HL_HAND * 32 + lane] = E.hand;
@@ -396,36 +408,18 @@ __device__ __forceinline__ void env_store(const Env &E, u32 *rec, int lane, u32 
   rec[COG_HL_DISCARD * 32 + lane] = E.discard;
   rec[COG_HL_SHOP * 32 + lane] = E.shop;
   rec[COG_HL_NBR * 32 + lane] = E.nbr;
-  /* word 4 f + p <- field f of the lane that holds player p */
-  const int f = lane >> 2, q = lane & 3;
-  u32 pw = 0, t;
-  t = bcast(E.pf, q);    if (f == COG_PF_FLAGS) pw = t;
-  t = bcast(E.pc, q);    if (f == COG_PF_COUNTS) pw = t;
-  t = bcast(E.pmv, q);   if (f == COG_PF_MOVES) pw = t;
-  t = bcast(E.ploc, q);  if (f == COG_PF_LOC) pw = t;
-  t = bcast(E.Pplay, q); if (f == COG_PF_MPLAY) pw = t;
-  t = bcast(E.Prem, q);  if (f == COG_PF_MREM) pw = t;
-  t = bcast(E.Pms, q);   if (f == COG_PF_MMS) pw = t;
-  rec[COG_HL_PLAYER * 32 + lane] = pw;
-  u32 ew = 0;
-  switch (lane) {
-  case COG_ES_RNG: ew = E.rng; break;
-  case COG_ES_TURN: ew = E.turn; break;
-  case COG_ES_MISC: ew = E.agent | (E.phase << 8) | (E.n_in_market << 16); break;
-  case COG_ES_RES0: ew = (u32)E.res[0]; break;
-  case COG_ES_RES1: ew = (u32)E.res[1]; break;
-  case COG_ES_RES2: ew = (u32)E.res[2]; break;
-  case COG_ES_MIN: ew = loc_pack(E.minx, E.miny); break;
-  case COG_ES_SPLAY: ew = E.Splay; break;
-  case COG_ES_SREM: ew = E.Srem; break;
-  case COG_ES_SMS: ew = E.Sms; break;
-  case COG_ES_INFOSTEPS: ew = E.info_steps; break;
-  case COG_ES_CPF: ew = E.cpf; break;
-  case COG_ES_CPC: ew = E.cpc; break;
-  case COG_ES_PENDING: ew = pending; break;
-  default: break;
+  if (lane < 4) {
+    uint4 *pl = reinterpret_cast<uint4 *>(rec + COG_HL_PLAYER * 32 + COG_PF_STRIDE * lane);
+    pl[0] = make_uint4(E.pf, E.pc, E.pmv, E.ploc);
+    pl[1] = make_uint4(E.Pplay, 0u, E.Prem, E.Pms);
   }
-  rec[COG_HL_ENV * 32 + lane] = ew;
+  if (lane == 0) {
+    uint4 *ev = reinterpret_cast<uint4 *>(rec + COG_HL_ENV * 32);
+    ev[0] = make_uint4(E.rng, E.turn, E.agent | (E.phase << 8) | (E.n_in_market << 16), (u32)E.res[0]);
+    ev[1] = make_uint4((u32)E.res[1], (u32)E.res[2], loc_pack(E.minx, E.miny), E.Splay);
+    ev[2] = make_uint4(0u, E.Srem, E.Sms, E.info_steps);
+    ev[3] = make_uint4(E.cpf, E.cpc, pending, 0u);
+  }
 }
 
 /* ------------------------------------------------------------------ export */
@@ -444,9 +438,13 @@ __device__ __forceinline__ void export_mask(u8 *dst, u32 play, u32 spec, u32 rem
  * the players in `pmask` (bit p): phase, resources, shop stock, DeckObs[p], P[p], S */
 __device__ __forceinline__ void export_dynamic(const Env &E, const Buffers &B, u64 i, u32 pmask, int lane) {
   u8 *obs = B.obs + i * COGL_OBS_SIZE;
-  if (lane == 0) obs[COGL_OBS_PHASE] = (u8)E.phase;
-  if (lane < 3) /* no dynamic indexing of E.res: that would push the array to local memory */
-    reinterpret_cast<float *>(obs + COGL_OBS_RES)[lane] = 0.5f * (float)(lane == 0 ? E.res[0] : lane == 1 ? E.res[1] : E.res[2]);
+  /* phase (+ 3 bytes of record padding) and the three resource floats are 16 contiguous,
+   * 16-byte aligned bytes: one vector store of lane 0 */
+  static_assert(COGL_OBS_PHASE % 16 == 0 && COGL_OBS_RES == COGL_OBS_PHASE + 4, "shared tail of ObsData");
+  if (lane == 0)
+    *reinterpret_cast<uint4 *>(obs + COGL_OBS_PHASE) =
+        make_uint4(E.phase, __float_as_uint(0.5f * (float)E.res[0]), __float_as_uint(0.5f * (float)E.res[1]),
+                   __float_as_uint(0.5f * (float)E.res[2]));
   if (lane >= 1 && lane <= 18) obs[COGL_OBS_SHOP + lane - 1] = (u8)(E.shop & 0xffu);
   for (int p = 0; p < 4; ++p) {
     if (!((pmask >> p) & 1u)) continue;

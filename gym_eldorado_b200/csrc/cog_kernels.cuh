@@ -71,11 +71,10 @@ __global__ void __launch_bounds__(BLOCK_THREADS, 8) k_step_single(Buffers B, Par
   if (i >= n) return;
   Env E;
   env_load(E, B.hidden + i * COG_HID_WORDS, lane);
-  const u8 *a = actions_in + i * COGL_ACTION_SIZE;
-  const u32 mine = lane < 5 ? (u32)a[lane] : 0u;
-  const u32 act = bcast(mine, 0) | (bcast(mine, 1) << 8) | (bcast(mine, 2) << 16) | (bcast(mine, 3) << 24);
+  /* the five ActionData bytes: every lane reads the same 8 bytes (one transaction), no shuffles */
+  const uint2 a = *reinterpret_cast<const uint2 *>(actions_in + i * COGL_ACTION_SIZE);
   bool obs_pending = false;
-  const u32 status = env_step<false, false>(E, act, bcast(mine, 4), prm, B, i, obs_pending, lane);
+  const u32 status = env_step<false, false>(E, a.x, a.y & 0xffu, prm, B, i, obs_pending, lane);
   if (status & 1u) {
     env_finish_episode(E, prm, B, i, lane);
     env_reset(E, prm, B, i, warp_scratch(), lane);

@@ -39,8 +39,9 @@ enum {
  * line 5     shop: lane l (1..18) holds slot l-1: bits 0-7 n_available, bit 8 in_market
  * line 6     neighbour cache: lane d (0..6): byte r = hex code of the hex in direction d
  *            of player (agent + r) & 3 (d = 0: the hex the player stands on)
- * line 7     per-player fields, word 4*f + p = field f of player p (COG_PF_*)
- * line 8     env scalars, word = COG_ES_*
+ * line 7     per-player fields, word 8*p + f = field f of player p (COG_PF_*): a player's
+ *            fields are two 16-byte vectors
+ * line 8     env scalars, word = COG_ES_* (four 16-byte vectors)
  */
 enum {
   COG_HID_LINES = 9,
@@ -57,7 +58,8 @@ enum {
   COG_PF_LOC = 3,    /* int16 x | int16 y << 16, in half-hex units (2x the reference's float) */
   COG_PF_MPLAY = 4, COG_PF_MSPEC = 5 /* unused: play_special is derived from play */,
   COG_PF_MREM = 6, /* P[p] mask heads as bit sets */
-  COG_PF_MMS = 7     /* P[p].move (bits 0-6) | P[p].get_from_shop (bits 7-25) */
+  COG_PF_MMS = 7,    /* P[p].move (bits 0-6) | P[p].get_from_shop (bits 7-25) */
+  COG_PF_STRIDE = 8  /* words per player */
 };
 /* env scalars (line 8) */
 enum {
