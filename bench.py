@@ -401,9 +401,11 @@ def main():
             L.cog_vec_read(vec._h, layout.BUF_DONES, h_done.data_ptr(), h_done.numel())
             L.cog_vec_read(vec._h, layout.BUF_AGENT_SELECTION, h_agent.data_ptr(), h_agent.numel())
 
-        def e2e_step():  # same data flow, two calls, copies and kernels pipelined chunk by chunk
-            smp.sample_host_io(np_masks, np_actions)  # H2D masks -> sample -> D2H actions
-            vec.step_host_io(np_actions, np_masks, np_rew, np_done, np_agent)  # H2D actions -> step -> D2H results
+        def e2e_step():  # same data flow, two calls.  Pinned arrays: the kernels read the inputs from and
+            # write masks / actions to the host arrays themselves (zero copy); COG_IO_ZEROCOPY=0 or pageable
+            # arrays: staging copies and kernels pipelined chunk by chunk on two streams
+            smp.sample_host_io(np_masks, np_actions)  # host masks -> sample -> host actions
+            vec.step_host_io(np_actions, np_masks, np_rew, np_done, np_agent)  # host actions -> step -> host results
 
         def timed(fn, iters):
             for _ in range(5):
@@ -421,17 +423,27 @@ def main():
         e2e_iters = max(20, args.steps * 5)
         serial = timed(e2e_step_serial, e2e_iters)
         vec.read(layout.BUF_SELECTED_MASKS, np_masks)
+        os.environ["COG_IO_ZEROCOPY"] = "0"
         piped = timed(e2e_step, e2e_iters)
-        h2d = n * (mdt.itemsize + adt.itemsize)
-        d2h = n * (mdt.itemsize + adt.itemsize + 16 + 1 + 1)
-        e2e = {"value": piped, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+        os.environ.pop("COG_IO_ZEROCOPY")
+        vec.read(layout.BUF_SELECTED_MASKS, np_masks)
+        direct = timed(e2e_step, e2e_iters)
+        # bytes that cross the link per step on the zero-copy path: the kernels pull 3 of the 4 sectors of every
+        # ActionMask (92 payload bytes) and 1 of the 2 of every ActionData, and push 92 B of mask + 8 B of action;
+        # rewards / dones / agent_selection go by DMA.  (The DMA paths move the whole records: 192 B each way.)
+        h2d = n * (96 + 32)
+        d2h = n * (92 + 8 + 16 + 1 + 1)
+        full = n * (mdt.itemsize + adt.itemsize)
+        e2e = {"value": direct, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                "api": "host policy loop, every step: cog_sampler_sample_host_io(host masks -> host actions); "
                       "cog_vec_step_host_io(host actions -> host masks, rewards, dones, agent_selection); "
-                      "single-step kernels, pinned host buffers, copies and kernels pipelined in chunks on two "
-                      "streams, %d iterations" % e2e_iters,
-               "serial_calls_value": serial,
-               "pcie_bound": "%.1f MB per step cross PCIe (%.1f in, %.1f out): this loop is bound by the link, "
-                             "not by the kernels" % ((h2d + d2h) / 1e6, h2d / 1e6, d2h / 1e6)}
+                      "single-step kernels; the pinned host arrays are read and written by the kernels themselves "
+                      "over PCIe (no staging copies), small outputs by DMA; %d iterations" % e2e_iters,
+               "dma_pipeline_value": piped, "serial_calls_value": serial,
+               "dma_bytes_per_step": {"h2d": full, "d2h": full + n * 18},
+               "note": "dma_pipeline_value = the same calls with COG_IO_ZEROCOPY=0 (what pageable arrays get): "
+                       "staging copies + kernels pipelined in two chunks on two streams; serial_calls_value = one "
+                       "blocking call per copy / kernel"}
     launches = L.cog_kernel_launches() - launches0
 
     cpu = None

@@ -160,6 +160,29 @@ int pipe_run(Pipe &p, F enqueue) {
   CK(cudaStreamSynchronize(p.io[0]));          /* the host buffers are complete on return */
   return COG_OK;
 }
+/* Is `p` pinned host memory that kernels can address (cudaHostAlloc / cudaHostRegister under
+ * unified addressing — what torch's pin_memory() hands out)?  Then the *_host_io entry points
+ * skip the staging copies: the kernels read their inputs from, and write the bulky outputs to,
+ * the caller's arrays directly, and only the bytes that are needed cross PCIe (3 of the 4
+ * sectors of an ActionMask, 1 of the 2 of an ActionData).  COG_IO_ZEROCOPY=0 switches it off. */
+bool host_mapped(const void *p, void **dev) {
+  const char *e = std::getenv("COG_IO_ZEROCOPY");
+  if (e && e[0] == '0') return false;
+#ifdef COG_EMU
+  *dev = const_cast<void *>(p); /* the emulator's "device" is host memory */
+  return true;
+#else
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  if (a.type != cudaMemoryTypeHost || !a.devicePointer) return false;
+  *dev = a.devicePointer;
+  return true;
+#endif
+}
+
 uint64_t io_chunk(uint64_t n) {
   static const int chunks = [] { /* tunable: COG_IO_CHUNKS=1 disables the pipeline */
     const char *e = std::getenv("COG_IO_CHUNKS");
@@ -313,7 +336,7 @@ int cog_vec_step(cog_vec *h, const void *d_actions) {
   CK(cudaSetDevice(h->device));
   time_begin(h);
   COG_LAUNCH(cog::k_step_single, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B,
-             h->prm, (uint64_t)0, h->n, (const uint8_t *)d_actions);
+             h->prm, (uint64_t)0, h->n, (const uint8_t *)d_actions, (uint8_t *)nullptr);
   time_end(h);
   g_launches++;
   CK(cudaGetLastError());
@@ -419,7 +442,7 @@ int cog_sampler_sample(cog_sampler *s, const void *d_masks) {
   if (!s || !d_masks) return fail(COG_ERR_INVALID, "NULL argument");
   CK(cudaSetDevice(s->device));
   COG_LAUNCH(cog::k_sample, blocks_for(s->n), cog::BLOCK_THREADS, 0, s->stream, (const uint8_t *)d_masks,
-             s->srng, s->actions, s->n);
+             s->srng, s->actions, s->n, (uint8_t *)nullptr);
   g_launches++;
   CK(cudaGetLastError());
   return COG_OK;
@@ -459,6 +482,15 @@ int cog_vec_step_host(cog_vec *h, const void *h_actions) {
 int cog_sampler_sample_host_io(cog_sampler *s, const void *h_masks, void *h_actions_out) {
   if (!s || !h_masks || !h_actions_out) return fail(COG_ERR_INVALID, "NULL argument");
   CK(cudaSetDevice(s->device));
+  void *zm = nullptr, *za = nullptr;
+  if (host_mapped(h_masks, &zm) && host_mapped(h_actions_out, &za)) {
+    COG_LAUNCH(cog::k_sample, blocks_for(s->n), cog::BLOCK_THREADS, 0, s->stream, (const uint8_t *)zm, s->srng,
+               s->actions, s->n, (uint8_t *)za);
+    g_launches++;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(s->stream)); /* the host array is complete on return */
+    return COG_OK;
+  }
   if (!s->staging) CK(cudaMalloc(&s->staging, s->n * COG_MASK_SIZE));
   Pipe p{s->io, s->io_ev, s->stream};
   const uint64_t chunk = io_chunk(s->n);
@@ -470,7 +502,8 @@ int cog_sampler_sample_host_io(cog_sampler *s, const void *h_masks, void *h_acti
       uint8_t *d_a = s->actions + i0 * COG_ACTION_SIZE;
       CK(cudaMemcpyAsync(d_m, (const uint8_t *)h_masks + i0 * COG_MASK_SIZE, cnt * COG_MASK_SIZE,
                          cudaMemcpyHostToDevice, io[k]));
-      COG_LAUNCH(cog::k_sample, blocks_for(cnt), cog::BLOCK_THREADS, 0, io[k], d_m, s->srng + i0, d_a, cnt);
+      COG_LAUNCH(cog::k_sample, blocks_for(cnt), cog::BLOCK_THREADS, 0, io[k], d_m, s->srng + i0, d_a, cnt,
+                 (uint8_t *)nullptr);
       CK(cudaMemcpyAsync((uint8_t *)h_actions_out + i0 * COG_ACTION_SIZE, d_a, cnt * COG_ACTION_SIZE,
                          cudaMemcpyDeviceToHost, io[k]));
     }
@@ -485,6 +518,20 @@ int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, v
   if (!h || !h_actions) return fail(COG_ERR_INVALID, "NULL argument");
   if (!h->seeded) return fail(COG_ERR_NOT_RESET, "step() before reset()");
   CK(cudaSetDevice(h->device));
+  void *za = nullptr, *zm = nullptr;
+  if (host_mapped(h_actions, &za) && (!h_masks_out || host_mapped(h_masks_out, &zm))) {
+    COG_LAUNCH(cog::k_step_single, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm,
+               (uint64_t)0, h->n, (const uint8_t *)za, (uint8_t *)zm);
+    g_launches++;
+    CK(cudaGetLastError());
+    /* the small outputs by DMA (1.1 MB for 65 536 envs) */
+    if (h_rewards_out)
+      CK(cudaMemcpyAsync(h_rewards_out, h->B.rewards, h->n * 16, cudaMemcpyDeviceToHost, h->stream));
+    if (h_dones_out) CK(cudaMemcpyAsync(h_dones_out, h->B.dones, h->n, cudaMemcpyDeviceToHost, h->stream));
+    if (h_agents_out) CK(cudaMemcpyAsync(h_agents_out, h->B.agents, h->n, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return COG_OK;
+  }
   if (!h->act_staging) CK(cudaMalloc(&h->act_staging, h->n * COG_ACTION_SIZE));
   Pipe p{h->io, h->io_ev, h->stream};
   const uint64_t chunk = io_chunk(h->n);
@@ -497,7 +544,7 @@ int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, v
                          (const uint8_t *)h_actions + i0 * COG_ACTION_SIZE, cnt * COG_ACTION_SIZE,
                          cudaMemcpyHostToDevice, st));
       COG_LAUNCH(cog::k_step_single, blocks_for(cnt), cog::BLOCK_THREADS, scratch_bytes(), st, h->B, h->prm, i0,
-                 i0 + cnt, (const uint8_t *)h->act_staging);
+                 i0 + cnt, (const uint8_t *)h->act_staging, (uint8_t *)nullptr);
       if (h_masks_out)
         CK(cudaMemcpyAsync((uint8_t *)h_masks_out + i0 * COG_MASK_SIZE, h->B.masks + i0 * COG_MASK_SIZE,
                            cnt * COG_MASK_SIZE, cudaMemcpyDeviceToHost, st));

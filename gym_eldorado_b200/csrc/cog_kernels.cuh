@@ -63,9 +63,10 @@ __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed)
 /* vec_cog_env<N>::step(actions): one step per env from `actions` (ActionData[n], 64-byte
  * records), auto-reset included; exports only the records the step touched.  Works on the
  * envs [i0, n) (i0 a multiple of the warps per block): the host-buffer entry points run it
- * chunk by chunk so that copies and kernels of different chunks overlap. */
+ * chunk by chunk so that copies and kernels of different chunks overlap.  `actions_in` may be
+ * mapped pinned HOST memory (each warp pulls its 8 action bytes over PCIe itself). */
 __global__ void __launch_bounds__(BLOCK_THREADS, 8) k_step_single(Buffers B, Params prm, u64 i0, u64 n,
-                                                                  const u8 *__restrict__ actions_in) {
+                                                                  const u8 *__restrict__ actions_in, u8 *masks2) {
   const int lane = threadIdx.x & 31;
   const u64 i = i0 + (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
   if (i >= n) return;
@@ -81,6 +82,9 @@ __global__ void __launch_bounds__(BLOCK_THREADS, 8) k_step_single(Buffers B, Par
   }
   env_store(E, B.hidden + i * COG_HID_WORDS, lane);
   export_dynamic(E, B, i, status >> 8, lane);
+  /* host-buffer entry point with mapped pinned memory: selected_action_masks goes straight to
+   * the caller's host array as well (92 contiguous bytes per env, posted writes over PCIe) */
+  if (masks2) export_mask(masks2 + i * COGL_MASK_SIZE, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, lane);
   if (lane == 0) {
     B.dones[i] = (u8)(status & 1u);
     if ((i & (WARPS_PER_BLOCK - 1)) == 0) { /* one atomic per block */
@@ -299,25 +303,37 @@ __global__ void k_compact_obs(Buffers B, Params prm, u64 n, u8 *out, int merged)
   compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), rem, ms, 0u, 0u, 0u, lane);
 }
 
-/* vec_action_sampler<N>::sample include/vec_sampler.h:14-21 on ActionMask[n] records:
- * lane k reads bool k of each head, a ballot turns the head into a bit set. */
-__global__ void k_sample(const u8 *__restrict__ masks, u32 *srng, u8 *actions, u64 n) {
+/* vec_action_sampler<N>::sample include/vec_sampler.h:14-21 on ActionMask[n] records.
+ * The 92 payload bytes of a record are read ONCE, as 23 words by 23 lanes (three 32-byte
+ * sectors — `masks` may be mapped pinned host memory, then these are the bytes that cross
+ * PCIe); lane k then fetches bool k of each head from the lane that holds its word, and a
+ * ballot turns the head into a bit set.  actions2 (optional): a second destination for the
+ * ActionData bytes, e.g. the caller's mapped host array. */
+__global__ void k_sample(const u8 *__restrict__ masks, u32 *srng, u8 *actions, u64 n, u8 *actions2) {
   const int lane = threadIdx.x & 31;
   const u64 i = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
   if (i >= n) return;
-  const u8 *m = masks + i * COGL_MASK_SIZE;
-  const bool in22 = lane < 22;
-  const u32 play = __ballot_sync(COG_FULL, in22 && m[COGL_AM_PLAY + lane]);
-  const u32 spec = __ballot_sync(COG_FULL, in22 && m[COGL_AM_SPECIAL + lane]);
-  const u32 rem = __ballot_sync(COG_FULL, in22 && m[COGL_AM_REMOVE + lane]);
-  const u32 move = __ballot_sync(COG_FULL, lane < 7 && m[COGL_AM_MOVE + lane]);
-  const u32 shop = __ballot_sync(COG_FULL, lane < 19 && m[COGL_AM_SHOP + lane]);
-  u32 sr = srng[i], act, a_shop;
+  const u32 *m = reinterpret_cast<const u32 *>(masks + i * COGL_MASK_SIZE);
+  const u32 w = lane < 23 ? m[lane] : 0u;
+  u32 sr = srng[i];
+  /* bool (base + lane) of the record = byte ((base + lane) & 3) of word (base + lane) >> 2 */
+#define COG_HEAD(base, count) \
+  __ballot_sync(COG_FULL, ((__shfl_sync(COG_FULL, w, ((base) + lane) >> 2) >> (8 * (((base) + lane) & 3))) & 0xffu) && \
+                              lane < (count))
+  const u32 play = COG_HEAD(COGL_AM_PLAY, 22);
+  const u32 spec = COG_HEAD(COGL_AM_SPECIAL, 22);
+  const u32 rem = COG_HEAD(COGL_AM_REMOVE, 22);
+  const u32 move = COG_HEAD(COGL_AM_MOVE, 7);
+  const u32 shop = COG_HEAD(COGL_AM_SHOP, 19);
+#undef COG_HEAD
+  u32 act, a_shop;
   sample_action(sr, play, spec, rem, move | (shop << 7), act, a_shop, lane);
   __syncwarp(); /* every lane has read srng[i] before lane 0 overwrites it */
-  if (lane == 0) srng[i] = sr;
-  if (lane < 4) actions[i * COGL_ACTION_SIZE + lane] = (u8)(act >> (8 * lane));
-  if (lane == 4) actions[i * COGL_ACTION_SIZE + 4] = (u8)a_shop;
+  if (lane == 0) {
+    srng[i] = sr;
+    *reinterpret_cast<uint2 *>(actions + i * COGL_ACTION_SIZE) = make_uint2(act, a_shop);
+    if (actions2) *reinterpret_cast<uint2 *>(actions2 + i * COGL_ACTION_SIZE) = make_uint2(act, a_shop);
+  }
 }
 
 /* vec_action_sampler<N>(seed) include/vec_sampler.h:9-13: set_seed(seed + i) on a

@@ -189,24 +189,40 @@ def run_fused_merged_parity(library, oracle_cls, n, seed, difficulty, max_steps,
         o.close()
 
 
-def run_host_io_parity(library, oracle_cls, n, seed, difficulty, max_steps, steps, regime="A"):
-    """The pipelined host-buffer entry points (cog_sampler_sample_host_io, cog_vec_step_host_io)
-    driven like the reference's Python loop — masks and actions only ever live in host arrays —
-    against the oracle."""
+def _host_array(shape, dtype, pinned):
+    """Zeroed host array; pinned=True: page-locked memory the kernels can address (torch's
+    pin_memory()), which takes the zero-copy branch of the *_host_io entry points."""
+    if not pinned:
+        return np.zeros(shape, dtype=dtype)
+    import torch
+    dt = np.dtype(dtype)
+    count = int(np.prod(shape))
+    t = torch.zeros(count * dt.itemsize, dtype=torch.uint8).pin_memory()
+    return t.numpy().view(dt).reshape(shape)  # the view keeps the pinned tensor alive through .base
+
+
+def run_host_io_parity(library, oracle_cls, n, seed, difficulty, max_steps, steps, regime="A", pinned=False):
+    """The host-buffer entry points (cog_sampler_sample_host_io, cog_vec_step_host_io) driven like
+    the reference's Python loop — masks and actions only ever live in host arrays — against the
+    oracle.  Pageable arrays go through the chunked copy/compute pipeline, pinned ones are read
+    and written by the kernels directly."""
     o = oracle_cls(n, seed)
     c = Candidate(library, n, seed)
     try:
         o.reset(seed, 4, 3, difficulty, max_steps)
         c.reset(seed, 4, 3, difficulty, max_steps)
-        masks = c.vec.read(layout.BUF_SELECTED_MASKS)
-        actions = np.zeros(n, dtype=layout.action_dtype)
-        rewards = np.zeros((n, 4), dtype=np.float32)
-        dones = np.zeros(n, dtype=np.bool_)
-        agents = np.zeros(n, dtype=np.uint8)
+        masks = _host_array(n, layout.action_mask_dtype, pinned)
+        c.vec.read(layout.BUF_SELECTED_MASKS, out=masks)
+        actions = _host_array(n, layout.action_dtype, pinned)
+        rewards = _host_array((n, 4), np.float32, pinned)
+        dones = _host_array(n, np.bool_, pinned)
+        agents = _host_array(n, np.uint8, pinned)
+        merged = _host_array(n, layout.action_mask_dtype, pinned)
         n_done = 0
         for s in range(steps):
             if regime == "M":
-                m = merged_masks(c.snapshot())
+                merged[...] = merged_masks(c.snapshot())
+                m = merged
                 o.sample(m)
             else:
                 m = masks

@@ -55,8 +55,12 @@ def test_emulated_fused_merged_masks(emu, oracle_cls):
     assert st["env_steps"] == 12 * 438
 
 
-def test_emulated_host_io(emu, oracle_cls):
-    assert parity.run_host_io_parity(emu, oracle_cls, 10, 5, layout.HARD, 6, 120) > 0
+@pytest.mark.parametrize("zero_copy,regime", [("1", "A"), ("0", "A"), ("1", "M")])
+def test_emulated_host_io(emu, oracle_cls, monkeypatch, zero_copy, regime):
+    # both branches of the *_host_io entry points: kernels addressing the caller's arrays directly
+    # (what pinned memory gets on the GPU) and the chunked copy/compute pipeline
+    monkeypatch.setenv("COG_IO_ZEROCOPY", zero_copy)
+    assert parity.run_host_io_parity(emu, oracle_cls, 10, 5, layout.HARD, 6, 120, regime) > 0
 
 
 @pytest.mark.parametrize("merged,difficulty,max_steps,n_players,chunks,n_slots", [

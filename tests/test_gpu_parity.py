@@ -143,11 +143,12 @@ def test_fused_merged_masks(cuda_lib, oracle_cls, n, difficulty, max_steps, n_pl
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n,regime", [(20000, "A"), (9001, "M")])
-def test_host_io_pipeline(cuda_lib, oracle_cls, n, regime):
+@pytest.mark.parametrize("n,regime,pinned", [(20000, "A", False), (9001, "M", False), (20000, "A", True),
+                                             (9001, "M", True)])
+def test_host_io_pipeline(cuda_lib, oracle_cls, n, regime, pinned):
     """sample / step through HOST buffers with chunked copy/compute overlap (several chunks,
     a ragged last one) == the oracle at every step."""
-    assert parity.run_host_io_parity(cuda_lib, oracle_cls, n, 99, layout.HARD, 10, 150, regime) > 0
+    assert parity.run_host_io_parity(cuda_lib, oracle_cls, n, 99, layout.HARD, 10, 150, regime, pinned=pinned) > 0
 
 
 @pytest.mark.gpu
