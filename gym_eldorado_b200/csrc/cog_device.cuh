@@ -320,19 +320,6 @@ __device__ __forceinline__ void env_rotate(Env &E, u32 r) {
   E.nbr = rotb(E.nbr, r);
   E.info_steps = rotb(E.info_steps, r);
 }
-/* Re-broadcast the warp-uniform fields from lane 0.  The values do not change; what changes
- * is that ptxas can PROVE them uniform again (a shuffle from a fixed lane), which it cannot
- * for values that came back through memory from an out-of-line call.  With uniform loop
- * state the step loop needs no BSSY/BSYNC pairs and no BRA.DIV guards before its shuffles. */
-__device__ __forceinline__ void env_uniform(Env &E) {
-  E.rng = bcast(E.rng, 0); E.turn = bcast(E.turn, 0); E.agent = bcast(E.agent, 0);
-  E.phase = bcast(E.phase, 0); E.n_in_market = bcast(E.n_in_market, 0);
-  E.cpf = bcast(E.cpf, 0); E.cpc = bcast(E.cpc, 0); E.info_steps = bcast(E.info_steps, 0);
-  E.Splay = bcast(E.Splay, 0); E.Srem = bcast(E.Srem, 0); E.Sms = bcast(E.Sms, 0);
-  E.res[0] = (int)bcast((u32)E.res[0], 0); E.res[1] = (int)bcast((u32)E.res[1], 0);
-  E.res[2] = (int)bcast((u32)E.res[2], 0);
-  E.minx = (int)bcast((u32)E.minx, 0); E.miny = (int)bcast((u32)E.miny, 0);
-}
 __device__ __forceinline__ int loc_x(u32 w) { return (int)(int16_t)(w & 0xffffu); }
 __device__ __forceinline__ int loc_y(u32 w) { return (int)(int16_t)(w >> 16); }
 __device__ __forceinline__ u32 loc_pack(int x, int y) {
@@ -945,7 +932,8 @@ __device__ __forceinline__ int bg_generate(BoardScratch &sc, BoardState &st, u32
                                            int difficulty, int lane) {
   enum { F_ENTER = 0, F_LOOP = 1, F_DONE = 2, MAX_DEPTH = 5 };
   /* the running frame lives in registers; parents wait on a small stack.  Popped values go
-   * through a broadcast so that they stay provably warp-uniform (see env_uniform) */
+   * through a broadcast so that ptxas can still prove them warp-uniform (a shuffle from a fixed
+   * lane is uniform by construction; a value that came back through local memory is not) */
   u32 s_rng[MAX_DEPTH];
   u64 s_valid[MAX_DEPTH];
   int s_nvalid[MAX_DEPTH], s_i[MAX_DEPTH], s_state[MAX_DEPTH];
