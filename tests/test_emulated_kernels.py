@@ -75,3 +75,36 @@ def test_emulated_rollout_and_compact_obs(emu, oracle_cls, merged, difficulty, m
     assert dones > 0
     if max_steps > 100:
         assert wins > 0
+
+
+def test_emulated_error_behaviour_of_the_additions(emu, oracle_cls):
+    """Argument / state errors of the entry points that are not in the reference: they report
+    through cog_last_error like the rest of the C ABI and leave the handle usable."""
+    c = parity.Candidate(emu, 5, 1)  # 5 envs: a ragged last block
+    try:
+        with pytest.raises(capi.CogError) as e:
+            c.vec.compact_obs()
+        assert e.value.code == capi.COG_ERR_NOT_RESET
+        with pytest.raises(capi.CogError):
+            c.vec.read_rollout()                  # no ring attached
+        c.reset(1, 4, 3, layout.EASY, 100000)
+        with pytest.raises(capi.CogError) as e:
+            c.vec.rollout_attach(0xffffffff)      # n_envs * n_slots must fit 32 bits
+        assert e.value.code == capi.COG_ERR_INVALID
+        assert c.vec.rollout_info() == (None, 0, 0)
+        c.vec.rollout_attach(1)                   # a ring of one slot keeps the latest step
+        c.vec.run_fused(c.smp, 7)
+        ring = c.vec.read_rollout()
+        assert ring.shape == (5, 1) and (ring["t"] == 6).all() and (ring["filled"] == 1).all()
+        c.vec.rollout_attach(3)                   # re-attach: counters restart
+        assert c.vec.rollout_info()[1:] == (3, 0)
+        c.vec.run_fused(c.smp, 0)                 # zero iterations: nothing recorded
+        assert c.vec.rollout_info()[2] == 0
+        o = oracle_cls(5, 1)
+        o.reset(1, 4, 3, layout.EASY, 100000)
+        for _ in range(7):
+            o.sample(); o.step()
+        assert parity.first_mismatch(c.snapshot(), parity.oracle_snapshot(o)) is None
+        o.close()
+    finally:
+        c.close()
