@@ -162,14 +162,18 @@ template <bool MERGED, bool ROLLOUT>
 __global__ void __launch_bounds__(BLOCK_THREADS, ROLLOUT ? (MERGED ? COG_RING_BLOCKS_MERGED : COG_RING_BLOCKS) : COG_MIN_BLOCKS) k_step_fused(Buffers B, Params prm, u64 n, u32 *srng,
                                                                              u8 *actions_out, u32 k_steps, Rollout R) {
   const int lane = threadIdx.x & 31;
-#ifdef COG_UNIFORM_PROOF
-  /* EXPERIMENT, off by default.  With the warp index taken through a shuffle from a fixed
-   * lane ptxas can prove the env loop and all env scalars warp-uniform and drops every
-   * BSSY/BSYNC pair and BRA.DIV guard from the loop (+8 % on the B200).  But the code it
-   * then emits keeps the loop counters in uniform registers and miscounts them as soon as
-   * episodes end with several envs per warp (CUDA 12.9, sm_100a): envs parked with wrong
-   * counts, steps counted twice.  tests/test_gpu_parity.py::test_fused_equals_single_steps
-   * (12000 envs) catches it.  Not used until that is understood. */
+#ifndef COG_NO_UNIFORM_PROOF
+  /* The warp index goes through a shuffle from a fixed lane.  The value is the same, but now
+   * ptxas can PROVE the env loop — and, with the re-broadcast after env_load below, every env
+   * scalar — warp-uniform: it drops the BSSY/BSYNC pairs and BRA.DIV guards from the step loop
+   * (178 -> 24 and 51 -> 0 in the kernel, 3 976 -> 2 880 instructions) and moves scalar work
+   * to the uniform datapath, off the ALU pipe that bounds this kernel (+5 % env-steps/s).
+   * The proof is fragile (it also depends on the loop-carried counters below being there:
+   * without them ptxas falls back to divergent code) and an earlier layout of the kernel
+   * produced wrong counters in this mode, so the result is pinned by tests:
+   * tests/test_gpu_parity.py::test_fused_equals_single_steps (12000 envs: several envs per warp,
+   * episodes ending inside the launch) and tools/variant_check.py against a build with
+   * -DCOG_NO_UNIFORM_PROOF. */
   const u64 warp0 = (u64)blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0);
 #else
   const u64 warp0 = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
@@ -181,6 +185,17 @@ __global__ void __launch_bounds__(BLOCK_THREADS, ROLLOUT ? (MERGED ? COG_RING_BL
     Env E;
     env_load(E, B.hidden + i * COG_HID_WORDS, lane);
     u32 sr = srng[i];
+#ifndef COG_NO_UNIFORM_PROOF
+    /* the same values, provably warp-uniform again (loads are not, shuffles from lane 0 are) */
+    E.rng = bcast(E.rng, 0); E.turn = bcast(E.turn, 0); E.agent = bcast(E.agent, 0);
+    E.phase = bcast(E.phase, 0); E.n_in_market = bcast(E.n_in_market, 0);
+    E.cpf = bcast(E.cpf, 0); E.cpc = bcast(E.cpc, 0); E.info_steps = bcast(E.info_steps, 0);
+    E.Splay = bcast(E.Splay, 0); E.Srem = bcast(E.Srem, 0); E.Sms = bcast(E.Sms, 0);
+    E.res[0] = (int)bcast((u32)E.res[0], 0); E.res[1] = (int)bcast((u32)E.res[1], 0);
+    E.res[2] = (int)bcast((u32)E.res[2], 0);
+    E.minx = (int)bcast((u32)E.minx, 0); E.miny = (int)bcast((u32)E.miny, 0);
+    sr = bcast(sr, 0);
+#endif
     u32 act = 0, a_shop = 0, status = 0;
     bool obs_pending = false;
     u32 k = k_steps;
