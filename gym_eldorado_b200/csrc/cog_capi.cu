@@ -16,6 +16,7 @@
 #endif
 
 #include <atomic>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -62,6 +63,23 @@ unsigned blocks_for(uint64_t n) { return (unsigned)((n + cog::WARPS_PER_BLOCK - 
 
 }  // namespace
 
+/* Which host-I/O path a handle uses for pinned arrays is measured, not assumed: on one GPU the
+ * zero-copy kernels win (fewer bytes cross PCIe), with eight ranks hammering the same host
+ * memory the staged DMA pipeline does.  Calls 0-1 warm the zero-copy path up, 2-4 time it,
+ * 5 warms the pipeline up, 6-8 time it; from call 9 on the faster one is used.  Both paths
+ * produce the same bytes.  COG_IO_ZEROCOPY=0 / 1 forces one of them. */
+struct IoTune {
+  int calls = 0, choice = -1; /* choice: 1 zero copy, 0 pipeline, -1 still measuring */
+  double t_zero = 0, t_pipe = 0;
+  bool use_zero() const { return choice >= 0 ? choice == 1 : calls < 5; }
+  void record(bool zero, double seconds) {
+    if (choice >= 0) return;
+    if (zero && calls >= 2) t_zero += seconds;
+    if (!zero && calls >= 6) t_pipe += seconds;
+    if (++calls == 9) choice = t_zero <= t_pipe ? 1 : 0;
+  }
+};
+
 struct cog_vec {
   uint64_t n = 0, offset = 0;
   int device = 0;
@@ -81,6 +99,7 @@ struct cog_vec {
   uint64_t ring_steps = 0;     /* env-steps per env recorded since attach; next slot = ring_steps % ring_slots */
   cudaStream_t io[2] = {nullptr, nullptr}; /* copy/compute pipeline of the *_host_io entry points */
   cudaEvent_t io_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  IoTune tune;
 };
 
 struct cog_sampler {
@@ -93,6 +112,7 @@ struct cog_sampler {
   void *staging = nullptr; /* device copy of host masks for cog_sampler_sample_host */
   cudaStream_t io[2] = {nullptr, nullptr};
   cudaEvent_t io_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  IoTune tune;
 };
 
 namespace {
@@ -165,9 +185,14 @@ int pipe_run(Pipe &p, F enqueue) {
  * skip the staging copies: the kernels read their inputs from, and write the bulky outputs to,
  * the caller's arrays directly, and only the bytes that are needed cross PCIe (3 of the 4
  * sectors of an ActionMask, 1 of the 2 of an ActionData).  COG_IO_ZEROCOPY=0 switches it off. */
-bool host_mapped(const void *p, void **dev) {
+int io_forced() { /* -1 measure, 0 pipeline, 1 zero copy */
   const char *e = std::getenv("COG_IO_ZEROCOPY");
-  if (e && e[0] == '0') return false;
+  return !e ? -1 : e[0] == '0' ? 0 : 1;
+}
+double now_seconds() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+bool host_mapped(const void *p, void **dev) {
 #ifdef COG_EMU
   *dev = const_cast<void *>(p); /* the emulator's "device" is host memory */
   return true;
@@ -483,12 +508,17 @@ int cog_sampler_sample_host_io(cog_sampler *s, const void *h_masks, void *h_acti
   if (!s || !h_masks || !h_actions_out) return fail(COG_ERR_INVALID, "NULL argument");
   CK(cudaSetDevice(s->device));
   void *zm = nullptr, *za = nullptr;
-  if (host_mapped(h_masks, &zm) && host_mapped(h_actions_out, &za)) {
+  const int forced = io_forced();
+  const bool eligible = forced != 0 && host_mapped(h_masks, &zm) && host_mapped(h_actions_out, &za);
+  const bool measuring = eligible && forced < 0 && s->tune.choice < 0;
+  const double t0 = measuring ? now_seconds() : 0.0;
+  if (eligible && (forced == 1 || s->tune.use_zero())) {
     COG_LAUNCH(cog::k_sample, blocks_for(s->n), cog::BLOCK_THREADS, 0, s->stream, (const uint8_t *)zm, s->srng,
                s->actions, s->n, (uint8_t *)za);
     g_launches++;
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(s->stream)); /* the host array is complete on return */
+    if (measuring) s->tune.record(true, now_seconds() - t0);
     return COG_OK;
   }
   if (!s->staging) CK(cudaMalloc(&s->staging, s->n * COG_MASK_SIZE));
@@ -510,6 +540,7 @@ int cog_sampler_sample_host_io(cog_sampler *s, const void *h_masks, void *h_acti
     return COG_OK;
   });
   g_launches += (s->n + chunk - 1) / chunk;
+  if (measuring && !rc) s->tune.record(false, now_seconds() - t0);
   return rc;
 }
 
@@ -519,7 +550,11 @@ int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, v
   if (!h->seeded) return fail(COG_ERR_NOT_RESET, "step() before reset()");
   CK(cudaSetDevice(h->device));
   void *za = nullptr, *zm = nullptr;
-  if (host_mapped(h_actions, &za) && (!h_masks_out || host_mapped(h_masks_out, &zm))) {
+  const int forced = io_forced();
+  const bool eligible = forced != 0 && host_mapped(h_actions, &za) && (!h_masks_out || host_mapped(h_masks_out, &zm));
+  const bool measuring = eligible && forced < 0 && h->tune.choice < 0;
+  const double t0 = measuring ? now_seconds() : 0.0;
+  if (eligible && (forced == 1 || h->tune.use_zero())) {
     COG_LAUNCH(cog::k_step_single, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm,
                (uint64_t)0, h->n, (const uint8_t *)za, (uint8_t *)zm);
     g_launches++;
@@ -530,6 +565,7 @@ int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, v
     if (h_dones_out) CK(cudaMemcpyAsync(h_dones_out, h->B.dones, h->n, cudaMemcpyDeviceToHost, h->stream));
     if (h_agents_out) CK(cudaMemcpyAsync(h_agents_out, h->B.agents, h->n, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
+    if (measuring) h->tune.record(true, now_seconds() - t0);
     return COG_OK;
   }
   if (!h->act_staging) CK(cudaMalloc(&h->act_staging, h->n * COG_ACTION_SIZE));
@@ -559,6 +595,7 @@ int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, v
     return COG_OK;
   });
   g_launches += (h->n + chunk - 1) / chunk;
+  if (measuring && !rc) h->tune.record(false, now_seconds() - t0);
   return rc;
 }
 
