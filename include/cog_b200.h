@@ -145,11 +145,19 @@ COG_API int cog_sampler_read_actions(cog_sampler *s, void *h_dst, size_t nbytes)
 
 /* Host-buffer forms of sample() / step() for callers whose policy lives on the host (the
  * reference's Python loop hands numpy arrays to vec_sampler.sample and vec_cog_env.step,
- * include/pybind/vectorized.h:60-68,107-127, and reads the views afterwards).  One call =
- * copy the inputs in, run, copy the results out, cut into two chunks (COG_IO_CHUNKS) on two
- * internal streams so that H2D, kernel and D2H of different chunks overlap; the host buffers are complete when
- * the call returns.  Pinned host memory is needed for the overlap (pageable memory works,
- * serialised).  Any *_out pointer of cog_vec_step_host_io may be NULL.
+ * include/pybind/vectorized.h:60-68,107-127, and reads the views afterwards).  The host buffers
+ * are complete when the call returns.  Two implementations, same bytes:
+ *  - staged: copy the inputs in, run, copy the results out, cut into two chunks (COG_IO_CHUNKS)
+ *    on two internal streams so that H2D, kernel and D2H of different chunks overlap (pinned
+ *    memory is needed for the overlap; pageable memory works, serialised);
+ *  - zero copy (pinned, device-addressable arrays only — cudaHostAlloc / cudaHostRegister, e.g.
+ *    torch's pin_memory()): the kernels read masks / actions from, and write actions / masks
+ *    to, the caller's arrays over PCIe themselves; only the needed sectors cross the link.
+ * For pinned arrays each handle times both on its first nine calls and keeps the faster one
+ * (zero copy on one GPU; the staged pipeline when eight ranks share one host's memory).
+ * COG_IO_ZEROCOPY=0 / 1 in the environment forces one.  The records must be aligned like the
+ * reference's (ActionMask 4 bytes, ActionData 8 bytes — any array of whole records is).
+ * Any *_out pointer of cog_vec_step_host_io may be NULL.
  *   h_masks / h_masks_out : ActionMask[n_envs]   h_actions / h_actions_out : ActionData[n_envs]
  *   h_rewards_out : float[n_envs][4]   h_dones_out : bool[n_envs]   h_agents_out : uint8[n_envs] */
 COG_API int cog_sampler_sample_host_io(cog_sampler *s, const void *h_masks, void *h_actions_out);
