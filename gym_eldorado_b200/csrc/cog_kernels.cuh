@@ -68,10 +68,26 @@ __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed)
 __global__ void __launch_bounds__(BLOCK_THREADS, 8) k_step_single(Buffers B, Params prm, u64 i0, u64 n,
                                                                   const u8 *__restrict__ actions_in, u8 *masks2) {
   const int lane = threadIdx.x & 31;
+#ifndef COG_NO_UNIFORM_PROOF
+  /* as in k_step_fused: warp index and env scalars through shuffles from a fixed lane, so that
+   * ptxas can prove them warp-uniform (BSSY 201 -> 111, BRA.DIV 68 -> 26, 6 624 -> 5 896
+   * instructions in this kernel; 76 -> 73 us per sample+step of 65 536 envs) */
+  const u64 i = i0 + (u64)blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0);
+#else
   const u64 i = i0 + (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+#endif
   if (i >= n) return;
   Env E;
   env_load(E, B.hidden + i * COG_HID_WORDS, lane);
+#ifndef COG_NO_UNIFORM_PROOF
+  E.rng = bcast(E.rng, 0); E.turn = bcast(E.turn, 0); E.agent = bcast(E.agent, 0);
+  E.phase = bcast(E.phase, 0); E.n_in_market = bcast(E.n_in_market, 0);
+  E.cpf = bcast(E.cpf, 0); E.cpc = bcast(E.cpc, 0); E.info_steps = bcast(E.info_steps, 0);
+  E.Splay = bcast(E.Splay, 0); E.Srem = bcast(E.Srem, 0); E.Sms = bcast(E.Sms, 0);
+  E.res[0] = (int)bcast((u32)E.res[0], 0); E.res[1] = (int)bcast((u32)E.res[1], 0);
+  E.res[2] = (int)bcast((u32)E.res[2], 0);
+  E.minx = (int)bcast((u32)E.minx, 0); E.miny = (int)bcast((u32)E.miny, 0);
+#endif
   /* the five ActionData bytes: every lane reads the same 8 bytes (one transaction), no shuffles */
   const uint2 a = *reinterpret_cast<const uint2 *>(actions_in + i * COGL_ACTION_SIZE);
   bool obs_pending = false;
@@ -326,11 +342,19 @@ __global__ void k_compact_obs(Buffers B, Params prm, u64 n, u8 *out, int merged)
  * ActionData bytes, e.g. the caller's mapped host array. */
 __global__ void k_sample(const u8 *__restrict__ masks, u32 *srng, u8 *actions, u64 n, u8 *actions2) {
   const int lane = threadIdx.x & 31;
+#ifndef COG_NO_UNIFORM_PROOF
+  const u64 i = (u64)blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0);
+#else
   const u64 i = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+#endif
   if (i >= n) return;
   const u32 *m = reinterpret_cast<const u32 *>(masks + i * COGL_MASK_SIZE);
   const u32 w = lane < 23 ? m[lane] : 0u;
+#ifndef COG_NO_UNIFORM_PROOF
+  u32 sr = bcast(srng[i], 0);
+#else
   u32 sr = srng[i];
+#endif
   /* bool (base + lane) of the record = byte ((base + lane) & 3) of word (base + lane) >> 2 */
 #define COG_HEAD(base, count) \
   __ballot_sync(COG_FULL, ((__shfl_sync(COG_FULL, w, ((base) + lane) >> 2) >> (8 * (((base) + lane) & 3))) & 0xffu) && \
