@@ -195,6 +195,13 @@ __constant__ const ud_entry UD_TAB[33] = {
     COG_UD(18), COG_UD(19), COG_UD(20), COG_UD(21), COG_UD(22), COG_UD(23), COG_UD(24), COG_UD(25), COG_UD(26),
     COG_UD(27), COG_UD(28), COG_UD(29), COG_UD(30), COG_UD(31), COG_UD(32)};
 
+/* r / e.scaling for r < e.past, without a division (exhaustively checked against the division for
+ * every n <= 32 and every engine output by tests/kat/prng_kat.cu) */
+__device__ __forceinline__ u32 ud_quotient(u32 r, const ud_entry &e) {
+  u32 q = __umulhi(r, e.magic) >> 4;
+  if (q * e.scaling > r) --q;
+  return q;
+}
 __device__ __forceinline__ u32 uniform_draw(u32 &s, u32 n) { /* n >= 1 */
   if (COG_LIKELY(n <= 32)) { /* n == 1: scaling = past = 2147483645, the result is 0 */
     const ud_entry e = UD_TAB[n];
@@ -202,9 +209,7 @@ __device__ __forceinline__ u32 uniform_draw(u32 &s, u32 n) { /* n >= 1 */
     do {
       r = minstd_next(s) - 1u;
     } while (COG_UNLIKELY(r >= e.past));
-    u32 q = __umulhi(r, e.magic) >> 4;
-    if (q * e.scaling > r) --q;
-    return q;
+    return ud_quotient(r, e);
   }
   const u32 scaling = 2147483645u / n;
   const u32 past = n * scaling;
@@ -423,7 +428,11 @@ __device__ __forceinline__ void export_mask(u8 *dst, u32 play, u32 spec, u32 rem
 
 /* everything a step can change in ObsData/ActionMask/agent_selection/Info, for
  * the players in `pmask` (bit p): phase, resources, shop stock, DeckObs[p], P[p], S */
-__device__ __forceinline__ void export_dynamic(const Env &E, const Buffers &B, u64 i, u32 pmask, int lane) {
+/* with_agent = false: vec_cog_env::reset() / reset(seed, ...) leave agent_selections[] alone — the array is
+ * only written by step_single (include/vec_environment.h:33-44,53-61), so after an explicit reset it
+ * still shows the agent of the last step */
+__device__ __forceinline__ void export_dynamic(const Env &E, const Buffers &B, u64 i, u32 pmask, int lane,
+                                               bool with_agent = true) {
   u8 *obs = B.obs + i * COGL_OBS_SIZE;
   /* phase (+ 3 bytes of record padding) and the three resource floats are 16 contiguous,
    * 16-byte aligned bytes: one vector store of lane 0 */
@@ -448,7 +457,7 @@ __device__ __forceinline__ void export_dynamic(const Env &E, const Buffers &B, u
     export_mask(pd + COGL_PD_MASK, Pplay, spec_of(Pplay), bcast(E.Prem, p), bcast(E.Pms, p), lane);
   }
   export_mask(B.masks + i * COGL_MASK_SIZE, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, lane);
-  if (lane == 0) B.agents[i] = (u8)E.agent;
+  if (with_agent && lane == 0) B.agents[i] = (u8)E.agent;
   if (lane < 4)
     B.infos[i * COGL_INFO_SIZE + COGL_INFO_AGENT + COGL_INFO_AGENT_STRIDE * lane] =
         (u8)getb(E.info_steps, rel(E, lane));
@@ -1397,9 +1406,7 @@ __device__ __forceinline__ u32 sample_head_warp(u32 &rng, u32 valid, int lane) {
   const u32 r = minstd_next(s1) - 1u;
   if (COG_UNLIKELY(r >= e.past)) return sample_head(rng, valid);
   rng = s1;
-  u32 q = __umulhi(r, e.magic) >> 4;
-  if (q * e.scaling > r) --q;
-  return nth_set_bit_warp(valid, q, lane);
+  return nth_set_bit_warp(valid, ud_quotient(r, e), lane);
 }
 /* The MERGED legal mask of the current agent: the reference splits
  * the truth over two records — play / play_special live in S, move / get_from_shop / remove in

@@ -57,7 +57,7 @@ __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed)
   if (reseed) E.rng = minstd_seed((u64)(u32)(seed_base + i));
   env_reset(E, prm, B, i, warp_scratch(), lane);
   env_store(E, B.hidden + i * COG_HID_WORDS, lane);
-  export_dynamic(E, B, i, 0xfu, lane);
+  export_dynamic(E, B, i, 0xfu, lane, false);
 }
 
 /* vec_cog_env<N>::step(actions): one step per env from `actions` (ActionData[n], 64-byte

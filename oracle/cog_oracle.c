@@ -4,7 +4,8 @@
  * reference file:line it follows (paths relative to the reference tree).
  * Coordinates are the reference's float axial hex coordinates multiplied by 2
  * (exact: every coordinate the reference produces is a multiple of 0.5).
- * PARITY PINNED against the compiled reference (tests/test_oracle_vs_reference.py).
+ * PARITY PINNED against the compiled reference and the golden vectors minted from it
+ * (tests/test_oracle.py).
  */
 #define _POSIX_C_SOURCE 200809L
 #include "cog_oracle.h"
@@ -347,6 +348,7 @@ typedef struct { /* cog_env (include/environment.h:13-33) + Shop + Map hidden st
   uint8_t *obs, *S, *info;
   float *rewards;
   uint64_t global_index; /* env_index_offset + i */
+  uint32_t n_start_b;    /* boards so far whose piece list holds start piece B (tests: SURVEY A#13) */
 } orc_env;
 
 struct orc_vec {
@@ -628,6 +630,8 @@ static int env_reset(orc_env *e, boardgen *bg) { /* cog_env::reset() :42-64 */
   bg_map_reset(bg);
   int rc = bg_generate(bg, e->n_pieces, e->difficulty, 0, e->rng); /* rng BY VALUE :48 */
   if (rc) return rc;
+  for (int k = 0; k < bg->n_list; ++k)
+    if (bg->list[k] == 1) { e->n_start_b++; break; }
   if (bg_finalize(bg, e->obs, 48, e->grid, ORC_GRID)) return -3;
   /* the reference would write outside its 48x48 observation (UB): report instead */
   if ((bg->maxx - bg->minx + 2) / 2 > 47 || (bg->maxy - bg->miny + 2) / 2 > 47) return -3;
@@ -915,5 +919,5 @@ void orc_hidden(orc_vec *v, uint64_t i, uint32_t *out) {
     out[5 + 2 * p] = (uint32_t)e->loc[p][1];
   }
   out[12] = (uint32_t)e->minx; out[13] = (uint32_t)e->miny;
-  out[14] = 0; out[15] = 0;
+  out[14] = e->n_start_b; out[15] = 0;
 }

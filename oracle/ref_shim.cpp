@@ -71,12 +71,28 @@ struct IVec {
 
 template <size_t N> struct VecImpl final : IVec {
   // heap: vec_cog_env<65536> is > 1 GiB
-  std::unique_ptr<vec_cog_env<N>> envs;
+  struct EnvDeleter;
+  std::unique_ptr<vec_cog_env<N>, EnvDeleter> envs;
   std::unique_ptr<vec_action_sampler<N>> samplers;
   std::unique_ptr<ThreadedRunner<N>> runner;
 
+  // The reference never initialises the Player slots of seats >= n_players, yet get_reward sums
+  // has_won over all four (src/environment.cpp:281-288, SURVEY A#10): with recycled heap memory a
+  // 2-player game can report garbage rewards.  The storage is zeroed before the reference's own
+  // constructor runs, i.e. every instance behaves like one on a fresh allocation.
+  static vec_cog_env<N> *fresh_envs() {
+    void *mem = ::operator new(sizeof(vec_cog_env<N>), std::align_val_t(alignof(vec_cog_env<N>)));
+    std::memset(mem, 0, sizeof(vec_cog_env<N>));
+    return new (mem) vec_cog_env<N>();
+  }
+  struct EnvDeleter {
+    void operator()(vec_cog_env<N> *p) const {
+      p->~vec_cog_env<N>();
+      ::operator delete(p, std::align_val_t(alignof(vec_cog_env<N>)));
+    }
+  };
   explicit VecImpl(uint64_t sampler_seed)
-      : envs(new vec_cog_env<N>()),
+      : envs(fresh_envs()),
         samplers(new vec_action_sampler<N>(static_cast<uint32_t>(sampler_seed))) {}
 
   size_t n() const override { return N; }

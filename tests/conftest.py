@@ -21,6 +21,18 @@ def oracle_cls():
     return port.OracleVec
 
 
+@pytest.fixture(scope="session", params=["port", "ref"])
+def gpu_oracle_cls(request):
+    """Both checkers for the GPU parity tests: the C restatement (oracle/cog_oracle.c) and the compiled
+    UNMODIFIED reference (oracle/_ref/libcog_ref.so); the test id says which one was used."""
+    if request.param == "port":
+        from oracle import port
+        port.build()
+        return port.OracleVec
+    import parity
+    return parity.ref_oracle_cls()
+
+
 @pytest.fixture(scope="session")
 def cuda_lib():
     """The product library. No fallback: a missing .so or device is an error, not a skip."""

@@ -336,3 +336,90 @@ def run_rollout_parity(library, oracle_cls, n, seed, difficulty, max_steps, chun
     finally:
         c.close()
         o.close()
+
+
+# ---- the compiled reference as a second oracle ---------------------------------------------
+def ref_oracle_cls():
+    """oracle/_ref/libcog_ref.so (the UNMODIFIED reference sources, oracle/Makefile) behind the
+    OracleVec surface, so that the GPU tests meet the reference's own outputs directly.  Cases the
+    reference cannot run are skipped, not faked: N outside the shim's template instantiations, fewer
+    than 4 players (heap overflow in Map::add_players, SURVEY A#13), boards of 6+ pieces (may write
+    outside the 48x48 observation)."""
+    import pytest
+    from oracle import port, refshim
+    if not refshim.available():
+        pytest.skip("oracle/_ref/libcog_ref.so not built (needs /root/reference at build time)")
+
+    class RefOracle(refshim.RefVec):
+        def __init__(self, n, sampler_seed, offset=0):
+            if n not in refshim.SUPPORTED_N:
+                pytest.skip("the reference shim instantiates N in %s only" % (refshim.SUPPORTED_N,))
+            base = (int(sampler_seed) & 0xFFFFFFFF) + offset
+            if base > 0xFFFFFFFF:
+                pytest.skip("sampler seed + offset does not fit the reference's 32-bit constructor argument")
+            self._offset = offset
+            super().__init__(n, base)
+
+        def reset(self, seed=None, n_players=4, n_pieces=3, difficulty=0, max_steps=100000):
+            if seed is not None:
+                if n_players < 4:
+                    pytest.skip("fewer than 4 players is undefined behaviour in the reference")
+                if n_pieces > 5:
+                    pytest.skip("boards of 6+ pieces can leave the reference's 48x48 observation (UB)")
+                seed = int(seed) + self._offset
+            try:
+                super().reset(seed, n_players, n_pieces, difficulty, max_steps)
+            except RuntimeError as e:
+                if "generate map" in str(e):
+                    raise port.MapGenerationError(str(e))
+                raise
+
+    return RefOracle
+
+
+def run_mid_episode_reset(make_candidate, oracle_cls, n, seed, difficulty, max_steps, before=70, after=120):
+    """>= 50 regime-M steps, reset() WITHOUT arguments in the middle of the episodes (SURVEY App. A#6/A#7:
+    `played`, idx_last_activated and n_in_market survive, the RNG streams continue), then on."""
+    o = oracle_cls(n, seed)
+    c = make_candidate(n, seed)
+    snap_c = c.snapshot if hasattr(c, "snapshot") else (lambda: oracle_snapshot(c))
+    try:
+        o.reset(seed, 4, 3, difficulty, max_steps)
+        c.reset(seed, 4, 3, difficulty, max_steps)
+        for phase, steps in (("before", before), ("after", after)):
+            for s in range(steps):
+                m = merged_masks(oracle_snapshot(o))
+                o.sample(m)
+                c.sample(m)
+                o.step()
+                c.step()
+                if s % 10 == 9 or s == steps - 1:
+                    bad = first_mismatch(snap_c(), oracle_snapshot(o))
+                    assert bad is None, "%s the reset, step %d: %s" % (phase, s, bad)
+            if phase == "before":
+                snap = oracle_snapshot(o)
+                # the reset really interrupts games: cards in play, purchases made
+                assert snap["observations"]["player_data"]["obs"]["active"].sum() > 0
+                o.reset()
+                c.reset()
+                bad = first_mismatch(snap_c(), oracle_snapshot(o))
+                assert bad is None, "right after reset(): " + bad
+    finally:
+        c.close()
+        o.close()
+
+
+def two_player_clean_seeds(seed, n, difficulty, max_steps, steps, want=12):
+    """Seeds s = seed + i of 2-player envs whose every board within `steps` regime-M steps drew start piece A,
+    screened with the C restatement (whose 2-player rule is defined for both start pieces)."""
+    from oracle import port
+    o = port.OracleVec(n, seed)
+    try:
+        o.reset(seed, 2, 3, difficulty, max_steps)
+        for _ in range(steps):
+            o.sample(merged_masks(oracle_snapshot(o)))
+            o.step()
+        clean = [i for i in range(n) if o.hidden(i)[14] == 0]
+    finally:
+        o.close()
+    return [seed + i for i in clean[:want]]

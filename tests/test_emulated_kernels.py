@@ -112,3 +112,60 @@ def test_emulated_error_behaviour_of_the_additions(emu, oracle_cls):
         o.close()
     finally:
         c.close()
+
+
+# ---- round 2: the GPU parity chain (tests/test_gpu_chain.py) at emulator sizes -----------------
+def test_emulated_golden_boards(emu):
+    """the kernels' board generation + map encode against the fixtures minted from the reference"""
+    import golden_util
+    golden_util.check_boards(lambda n: parity.Candidate(emu, n, 0), lambda c: c.snapshot())
+
+
+@pytest.mark.parametrize("name,steps", [("readme_A", 200), ("hard_reset_heavy_M", 250), ("easy_M", 250)])
+def test_emulated_golden_trajectory_prefix(emu, name, steps):
+    import golden_util
+    cfg = golden_util.TRAJECTORIES[name]
+    c = parity.Candidate(emu, cfg[0], cfg[1])
+    golden_util.check_trajectory(name, c, c.snapshot, parity.merged_masks, steps=steps)
+    c.close()
+
+
+@pytest.mark.parametrize("difficulty,n_pieces", [(layout.MEDIUM, 5), (layout.HARD, 8), (layout.MEDIUM, 8)])
+def test_emulated_boards_many_pieces(emu, oracle_cls, difficulty, n_pieces):
+    from oracle import port
+    for seed in (11, 4000):
+        o = oracle_cls(24, 0)
+        c = parity.Candidate(emu, 24, 0)
+        try:
+            o.reset(seed, 4, n_pieces, difficulty, 100)
+        except port.MapGenerationError:
+            with pytest.raises(capi.MapGenerationError):
+                c.reset(seed, 4, n_pieces, difficulty, 100)
+        else:
+            c.reset(seed, 4, n_pieces, difficulty, 100)
+            assert parity.first_mismatch(c.snapshot(), parity.oracle_snapshot(o)) is None
+        c.close(); o.close()
+
+
+def test_emulated_mid_episode_reset(emu, oracle_cls):
+    parity.run_mid_episode_reset(lambda n, seed: parity.Candidate(emu, n, seed), oracle_cls, 16, 4321, layout.EASY,
+                                 100000)
+
+
+def test_emulated_two_players_vs_reference(emu):
+    """the kernels against the compiled reference itself on 2-player games the reference defines"""
+    from oracle import refshim
+    if not refshim.available():
+        pytest.skip("oracle/_ref not built")
+    for seed in parity.two_player_clean_seeds(99000, 8192, layout.HARD, 20, 120, want=3):
+        r = refshim.RefVec(1, seed)
+        c = parity.Candidate(emu, 1, seed)
+        r.reset(seed, 2, 3, layout.HARD, 20)
+        c.reset(seed, 2, 3, layout.HARD, 20)
+        for s in range(120):
+            m = r.merged_masks()
+            r.sample(m); c.sample(m)
+            r.step(); c.step()
+            bad = parity.first_mismatch(c.snapshot(), parity.oracle_snapshot(r))
+            assert bad is None, "seed %d step %d: %s" % (seed, s, bad)
+        c.close(); r.close()

@@ -12,6 +12,14 @@ from gym_eldorado_b200.layout import payload_bytes as pb
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(scope="module")
+def oracle_cls(gpu_oracle_cls):
+    """every test of this module runs against BOTH checkers (ids [port] / [ref]): the C restatement and
+    the compiled unmodified reference; cases the reference cannot run (N it is not instantiated for,
+    fewer than 4 players) skip on [ref]"""
+    return gpu_oracle_cls
+
+
 @pytest.mark.parametrize("n,seed,difficulty,max_steps,steps,regime,n_players", [
     (16, 0, layout.EASY, 100000, 1000, "A", 4),        # BASELINE config 1 (README example)
     (256, 12345, layout.EASY, 100000, 2000, "A", 4),   # BASELINE config 2 (asv loop), every step
@@ -35,9 +43,9 @@ def test_seed_wraps_and_offsets(cuda_lib, oracle_cls):
 
 @pytest.mark.parametrize("difficulty", [layout.EASY, layout.MEDIUM, layout.HARD])
 def test_boards_on_reset(cuda_lib, oracle_cls, difficulty):
-    """Procedural board generation + 48x48x7 encode: 2048 boards per difficulty."""
-    n = 2048
-    for seed, n_pieces in ((1, 3), (500000, 2), (77, 1), (9000, 1)):
+    """Procedural board generation + 48x48x7 encode: 5 x 1024 boards per difficulty."""
+    n = 1024
+    for seed, n_pieces in ((1, 3), (3001, 3), (500000, 2), (77, 1), (9000, 1)):
         o = oracle_cls(n, 0)
         c = parity.Candidate(cuda_lib, n, 0)
         try:
@@ -70,7 +78,7 @@ def test_map_failure_is_reported(cuda_lib):
     c.close()
 
 
-@pytest.mark.parametrize("n,difficulty,max_steps,k", [(512, layout.MEDIUM, 100000, 300), (512, layout.HARD, 8, 300),
+@pytest.mark.parametrize("n,difficulty,max_steps,k", [(1024, layout.MEDIUM, 100000, 300), (1024, layout.HARD, 8, 300),
                                                       # more envs than resident warps: several envs per warp,
                                                       # episode ends parked for the tail kernel
                                                       (12000, layout.HARD, 8, 120), (12000, layout.EASY, 100000, 120)])
@@ -131,7 +139,7 @@ def test_full_size_properties(cuda_lib):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n,difficulty,max_steps,n_players", [(512, layout.EASY, 60, 4), (9000, layout.HARD, 40, 4),
+@pytest.mark.parametrize("n,difficulty,max_steps,n_players", [(1024, layout.EASY, 60, 4), (9000, layout.HARD, 40, 4),
                                                              (256, layout.MEDIUM, 100000, 3)])
 def test_fused_merged_masks(cuda_lib, oracle_cls, n, difficulty, max_steps, n_players):
     """The fused kernel sampling from the merged legal mask (moves, purchases, removals,

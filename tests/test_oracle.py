@@ -117,3 +117,45 @@ def test_seed_determinism(oracle_cls):
     b.reset(123, 3, 8, layout.MEDIUM, 200)
     assert np.array_equal(pb(a.observations), pb(b.observations))
     a.close(); b.close()
+
+
+# ---- round 2: the remaining links of the chain on the CPU side -------------------------------
+@pytest.mark.skipif(not refshim.available(), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("difficulty", [1, 2])
+def test_oracle_boards_many_pieces_match_compiled_reference(difficulty):
+    """boards of up to 8 travel pieces (SURVEY App. D: they reach the edge of the 48x48 grid), on an
+    oversized observation buffer so that the reference's writes stay in bounds"""
+    for seed in range(5000, 5120):
+        for n_pieces in (4, 6, 7, 8):
+            a = refshim.map_generate(seed, n_pieces, difficulty, rows=96)
+            b = port.map_generate(seed, n_pieces, difficulty, rows=96)
+            assert np.array_equal(a[0], b[0]) and np.array_equal(a[2], b[2]), (seed, n_pieces)
+            assert np.array_equal(a[1][:6], b[1][:6]), (seed, n_pieces)
+
+
+@pytest.mark.skipif(not refshim.available(), reason="oracle/_ref not built (needs /root/reference)")
+@pytest.mark.parametrize("difficulty,max_steps", [(layout.EASY, 100000), (layout.HARD, 40)])
+def test_oracle_mid_episode_reset_matches_compiled_reference(oracle_cls, difficulty, max_steps):
+    """SURVEY App. A#6/A#7: reset() in the middle of an episode, port against the compiled reference"""
+    parity.run_mid_episode_reset(lambda n, seed: oracle_cls(n, seed), refshim.RefVec, 64, 4321, difficulty, max_steps)
+
+
+@pytest.mark.skipif(not refshim.available(), reason="oracle/_ref not built (needs /root/reference)")
+def test_oracle_two_players_matches_compiled_reference(oracle_cls):
+    """2-player games where the reference is defined (every board in the window drew start piece A,
+    src/map.cpp:343-354, SURVEY A#13): the port's "player i starts on hex i" rule == the reference"""
+    seeds = parity.two_player_clean_seeds(99000, 8192, layout.HARD, 20, 120, want=12)
+    assert len(seeds) >= 6
+    for seed in seeds:
+        r = refshim.RefVec(1, seed)
+        o = oracle_cls(1, seed)
+        r.reset(seed, 2, 3, layout.HARD, 20)
+        o.reset(seed, 2, 3, layout.HARD, 20)
+        for s in range(120):
+            m = r.merged_masks()
+            r.sample(m); o.sample(m)
+            r.step(); o.step()
+            bad = parity.first_mismatch(parity.oracle_snapshot(o), parity.oracle_snapshot(r))
+            assert bad is None, "seed %d step %d: %s" % (seed, s, bad)
+        assert o.hidden(0)[14] == 0
+        r.close(); o.close()
