@@ -32,6 +32,7 @@ SYMBOLS = {
     "cog_vec_reset_default": (_int, [_vp]),
     "cog_vec_step": (_int, [_vp, _vp]),
     "cog_vec_step_host": (_int, [_vp, _vp]),
+    "cog_vec_step_sampled": (_int, [_vp, _vp]),
     "cog_vec_buffer": (_int, [_vp, _int, _P(_vp), _P(_sz), _P(_sz)]),
     "cog_vec_read": (_int, [_vp, _int, _vp, _sz]),
     "cog_vec_num_envs": (_int, [_vp, _P(_u64)]),
@@ -128,6 +129,10 @@ class VecHandle:
 
     def step_device(self, d_actions_ptr):
         check(self.L, self.L.cog_vec_step(self._h, d_actions_ptr))
+
+    def step_sampled(self, sampler):
+        """sample(selected_action_masks); step(sampled actions) as one kernel."""
+        check(self.L, self.L.cog_vec_step_sampled(self._h, sampler._s))
 
     def step_host(self, actions):
         assert actions.dtype == layout.action_dtype and actions.flags.c_contiguous and len(actions) == self.n

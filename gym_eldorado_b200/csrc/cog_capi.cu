@@ -100,6 +100,7 @@ struct cog_vec {
   cudaStream_t io[2] = {nullptr, nullptr}; /* copy/compute pipeline of the *_host_io entry points */
   cudaEvent_t io_ev[4] = {nullptr, nullptr, nullptr, nullptr};
   IoTune tune;
+  uint64_t host_steps = 0;     /* env-steps of single-step calls since the last stats reset (n per call) */
 };
 
 struct cog_sampler {
@@ -255,6 +256,7 @@ uint64_t cog_kernel_launches(void) { return g_launches.load(); }
 
 int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device, void *stream, cog_vec **out) {
   if (!out || n_envs == 0) return fail(COG_ERR_INVALID, "n_envs must be > 0 and out non-NULL");
+  if (n_envs >= (1ull << 31)) return fail(COG_ERR_INVALID, "n_envs must be below 2^31 per handle (shard the job)");
   CK(cudaSetDevice(device));
   cog_vec *h = new (std::nothrow) cog_vec;
   if (!h) return fail(COG_ERR_INVALID, "out of host memory");
@@ -360,9 +362,27 @@ int cog_vec_step(cog_vec *h, const void *d_actions) {
   if (!h->seeded) return fail(COG_ERR_NOT_RESET, "step() before reset()");
   CK(cudaSetDevice(h->device));
   time_begin(h);
-  COG_LAUNCH(cog::k_step_single, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B,
-             h->prm, (uint64_t)0, h->n, (const uint8_t *)d_actions, (uint8_t *)nullptr);
+  COG_LAUNCH(cog::k_step_single<false>, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B,
+             h->prm, (uint64_t)0, h->n, (const uint8_t *)d_actions, (uint8_t *)nullptr, (uint32_t *)nullptr,
+             (uint8_t *)nullptr);
   time_end(h);
+  h->host_steps += h->n;
+  g_launches++;
+  CK(cudaGetLastError());
+  return COG_OK;
+}
+
+int cog_vec_step_sampled(cog_vec *h, cog_sampler *s) {
+  if (!h || !s) return fail(COG_ERR_INVALID, "NULL argument");
+  if (s->n != h->n || s->device != h->device) return fail(COG_ERR_INVALID, "sampler and envs differ in size or device");
+  if (!h->seeded) return fail(COG_ERR_NOT_RESET, "step() before reset()");
+  CK(cudaSetDevice(h->device));
+  if (s->stream != h->stream) CK(cudaStreamSynchronize(s->stream));
+  time_begin(h);
+  COG_LAUNCH(cog::k_step_single<true>, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B,
+             h->prm, (uint64_t)0, h->n, (const uint8_t *)nullptr, (uint8_t *)nullptr, s->srng, s->actions);
+  time_end(h);
+  h->host_steps += h->n;
   g_launches++;
   CK(cudaGetLastError());
   return COG_OK;
@@ -424,6 +444,7 @@ int cog_vec_read(cog_vec *h, int which, void *h_dst, size_t nbytes) {
 int cog_sampler_create(uint64_t n_envs, uint64_t env_index_offset, uint32_t seed, int device, void *stream,
                        cog_sampler **out) {
   if (!out || n_envs == 0) return fail(COG_ERR_INVALID, "n_envs must be > 0 and out non-NULL");
+  if (n_envs >= (1ull << 31)) return fail(COG_ERR_INVALID, "n_envs must be below 2^31 per handle (shard the job)");
   CK(cudaSetDevice(device));
   cog_sampler *s = new (std::nothrow) cog_sampler;
   if (!s) return fail(COG_ERR_INVALID, "out of host memory");
@@ -555,8 +576,9 @@ int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, v
   const bool measuring = eligible && forced < 0 && h->tune.choice < 0;
   const double t0 = measuring ? now_seconds() : 0.0;
   if (eligible && (forced == 1 || h->tune.use_zero())) {
-    COG_LAUNCH(cog::k_step_single, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm,
-               (uint64_t)0, h->n, (const uint8_t *)za, (uint8_t *)zm);
+    COG_LAUNCH(cog::k_step_single<false>, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm,
+               (uint64_t)0, h->n, (const uint8_t *)za, (uint8_t *)zm, (uint32_t *)nullptr, (uint8_t *)nullptr);
+    h->host_steps += h->n;
     g_launches++;
     CK(cudaGetLastError());
     /* the small outputs by DMA (1.1 MB for 65 536 envs) */
@@ -579,8 +601,8 @@ int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, v
       CK(cudaMemcpyAsync((uint8_t *)h->act_staging + i0 * COG_ACTION_SIZE,
                          (const uint8_t *)h_actions + i0 * COG_ACTION_SIZE, cnt * COG_ACTION_SIZE,
                          cudaMemcpyHostToDevice, st));
-      COG_LAUNCH(cog::k_step_single, blocks_for(cnt), cog::BLOCK_THREADS, scratch_bytes(), st, h->B, h->prm, i0,
-                 i0 + cnt, (const uint8_t *)h->act_staging, (uint8_t *)nullptr);
+      COG_LAUNCH(cog::k_step_single<false>, blocks_for(cnt), cog::BLOCK_THREADS, scratch_bytes(), st, h->B, h->prm, i0,
+                 i0 + cnt, (const uint8_t *)h->act_staging, (uint8_t *)nullptr, (uint32_t *)nullptr, (uint8_t *)nullptr);
       if (h_masks_out)
         CK(cudaMemcpyAsync((uint8_t *)h_masks_out + i0 * COG_MASK_SIZE, h->B.masks + i0 * COG_MASK_SIZE,
                            cnt * COG_MASK_SIZE, cudaMemcpyDeviceToHost, st));
@@ -595,6 +617,7 @@ int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, v
     return COG_OK;
   });
   g_launches += (h->n + chunk - 1) / chunk;
+  if (!rc) h->host_steps += h->n;
   if (measuring && !rc) h->tune.record(false, now_seconds() - t0);
   return rc;
 }
@@ -712,6 +735,7 @@ int cog_vec_stats(cog_vec *h, uint64_t *out, size_t n) {
   CK(cudaSetDevice(h->device));
   CK(cudaMemcpyAsync(tmp, h->B.stats, sizeof tmp, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
+  tmp[COG_STAT_ENV_STEPS] += h->host_steps; /* single steps are counted here, fused launches on the device */
   for (size_t i = 0; i < n; ++i) out[i] = tmp[i];
   return COG_OK;
 }
@@ -720,6 +744,7 @@ int cog_vec_stats_reset(cog_vec *h) {
   if (!h) return fail(COG_ERR_INVALID, "NULL handle");
   CK(cudaSetDevice(h->device));
   CK(cudaMemsetAsync(h->B.stats, 0, COG_STAT_COUNT * sizeof(unsigned long long), h->stream));
+  h->host_steps = 0;
   return COG_OK;
 }
 

@@ -95,6 +95,82 @@ __device__ const int8_t CONN_BASE[4][6][2] = {
     {{0, 8}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}},
     {{-7, 10}, {-5, 10}, {-3, 10}, {7, -10}, {5, -10}, {3, -10}}};
 
+/* Footprints as bitmap rows.  The occupancy bitmap of board generation is indexed [x][y] in half-hex
+ * units, so a piece shape at rotation r is at most seven rows (distinct x) of a few bits each:
+ * row entry = dx (int8) | y0 (int8) << 8 | bits << 16, bit b <-> a hex at (dx, y0 + b).  A candidate
+ * position is tested with one shifted AND per row instead of one lookup per hex (37 for a large
+ * piece) — and every candidate takes the same seven steps, so the lanes never diverge.
+ * bbox = min dx | max dx << 8 | min y << 16 | max y << 24 (int8 each).
+ * conn[kind][j][r] = connection point j of table `kind` rotated r times (int8 x | int8 y << 8). */
+struct foot_tab {
+  u32 row[3][6][7];
+  u32 bbox[3][6];
+  unsigned short conn[4][6][6];
+  u32 bad; /* a shape did not fit seven rows of sixteen bits (checked at compile time) */
+};
+namespace tab {
+constexpr xy8 C_LARGE[37] = COG_COORDS_LARGE_INIT;
+constexpr xy8 C_SMALL[16] = COG_COORDS_SMALL_INIT;
+constexpr xy8 C_END[3] = COG_COORDS_END_INIT;
+constexpr int C_CONN[4][6][2] = {
+    {{8, 6}, {6, 8}, {0, 0}, {0, 0}, {0, 0}, {0, 0}},
+    {{3, 7}, {5, 5}, {7, 3}, {0, 0}, {0, 0}, {0, 0}},
+    {{0, 8}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}},
+    {{-7, 10}, {-5, 10}, {-3, 10}, {7, -10}, {5, -10}, {3, -10}}};
+constexpr void rot60(int &x, int &y, int times) { /* (x, y) -> (-y, x + y), `times` times */
+  for (int t = 0; t < times; ++t) {
+    const int nx = -y, ny = x + y;
+    x = nx;
+    y = ny;
+  }
+}
+constexpr foot_tab make_foot() {
+  foot_tab f{};
+  for (int s = 0; s < 3; ++s) {
+    const xy8 *co = s == 0 ? C_LARGE : (s == 1 ? C_SMALL : C_END);
+    const int nh = s == 0 ? 37 : (s == 1 ? 16 : 3);
+    for (int r = 0; r < 6; ++r) {
+      int xs[40] = {}, ys[40] = {};
+      int minx = 127, maxx = -127, miny = 127, maxy = -127;
+      for (int h = 0; h < nh; ++h) {
+        int x = co[h].x, y = co[h].y;
+        rot60(x, y, r);
+        xs[h] = x;
+        ys[h] = y;
+        minx = x < minx ? x : minx; maxx = x > maxx ? x : maxx;
+        miny = y < miny ? y : miny; maxy = y > maxy ? y : maxy;
+      }
+      f.bbox[s][r] = (u32)(minx & 0xff) | ((u32)(maxx & 0xff) << 8) | ((u32)(miny & 0xff) << 16) | ((u32)(maxy & 0xff) << 24);
+      int n_rows = 0;
+      for (int x = minx; x <= maxx; ++x) {
+        int y0 = 127;
+        for (int h = 0; h < nh; ++h)
+          if (xs[h] == x && ys[h] < y0) y0 = ys[h];
+        if (y0 == 127) continue; /* no hex in this row */
+        u32 bits = 0;
+        for (int h = 0; h < nh; ++h)
+          if (xs[h] == x) bits |= 1u << (ys[h] - y0);
+        if (n_rows >= 7 || bits > 0xffffu) {
+          f.bad = 1;
+          continue;
+        }
+        f.row[s][r][n_rows++] = (u32)(x & 0xff) | ((u32)(y0 & 0xff) << 8) | (bits << 16);
+      }
+    }
+  }
+  for (int k = 0; k < 4; ++k)
+    for (int j = 0; j < 6; ++j)
+      for (int r = 0; r < 6; ++r) {
+        int x = C_CONN[k][j][0], y = C_CONN[k][j][1];
+        rot60(x, y, r);
+        f.conn[k][j][r] = (unsigned short)((x & 0xff) | ((y & 0xff) << 8));
+      }
+  return f;
+}
+}  // namespace tab
+static_assert(tab::make_foot().bad == 0, "piece footprints must fit seven bitmap rows of sixteen bits");
+__device__ const foot_tab FOOT = tab::make_foot();
+
 enum { SIZE_LARGE = 0, SIZE_SMALL = 1, SIZE_TRIPLE = 2 };
 enum { TYPE_START = 0, TYPE_TRAVEL = 1, TYPE_END = 2 };
 enum { PH_INACTIVE = 0, PH_MOVEMENT = 1, PH_BUYING = 2, PH_MAX = 3 };
@@ -351,25 +427,10 @@ __device__ __forceinline__ uint4 hid_vec(const u32 *rec, int w) {
  * env scalars are read as 16-byte vectors straight from the addresses every lane needs (lane l
  * wants the fields of player l & 3 and all sixteen scalars) — same-address lanes share one
  * transaction, so this is 6 vector loads instead of 2 loads + 27 shuffles. */
+/* the env scalars (line 8) and this lane's card / shop-slot constants */
 template <bool L2 = false>
-__device__ __forceinline__ void env_load(Env &E, const u32 *rec, int lane) {
+__device__ __forceinline__ void env_load_scalars(Env &E, const u32 *rec, int lane) {
   E.lc = LANE_CONST[lane];
-  E.draw = hid_word<L2>(rec, COG_HL_DRAW * 32 + lane);
-  E.hand = hid_word<L2>(rec, COG_HL_HAND * 32 + lane);
-  E.active = hid_word<L2>(rec, COG_HL_ACTIVE * 32 + lane);
-  E.played = hid_word<L2>(rec, COG_HL_PLAYED * 32 + lane);
-  E.discard = hid_word<L2>(rec, COG_HL_DISCARD * 32 + lane);
-  E.shop = hid_word<L2>(rec, COG_HL_SHOP * 32 + lane);
-  E.nbr = hid_word<L2>(rec, COG_HL_NBR * 32 + lane);
-  const int pbase = COG_HL_PLAYER * 32 + COG_PF_STRIDE * (lane & 3);
-  const uint4 p0 = hid_vec<L2>(rec, pbase), p1 = hid_vec<L2>(rec, pbase + 4);
-  E.pf = p0.x;    /* COG_PF_FLAGS */
-  E.pc = p0.y;    /* COG_PF_COUNTS */
-  E.pmv = p0.z;   /* COG_PF_MOVES */
-  E.ploc = p0.w;  /* COG_PF_LOC */
-  E.Pplay = p1.x; /* COG_PF_MPLAY */
-  E.Prem = p1.z;  /* COG_PF_MREM */
-  E.Pms = p1.w;   /* COG_PF_MMS */
   const uint4 e0 = hid_vec<L2>(rec, COG_HL_ENV * 32), e1 = hid_vec<L2>(rec, COG_HL_ENV * 32 + 4);
   const uint4 e2 = hid_vec<L2>(rec, COG_HL_ENV * 32 + 8), e3 = hid_vec<L2>(rec, COG_HL_ENV * 32 + 12);
   E.rng = e0.x;  /* COG_ES_RNG */
@@ -389,9 +450,70 @@ __device__ __forceinline__ void env_load(Env &E, const u32 *rec, int lane) {
   E.cpf = e3.x;   /* COG_ES_CPF */
   E.cpc = e3.y;   /* COG_ES_CPC */
 }
+/* the per-lane lines in `lines` (bit COG_HL_*) and, with bit COG_HL_PLAYER, the player line */
+template <u32 LINES, bool L2 = false>
+__device__ __forceinline__ void env_load_lines(Env &E, const u32 *rec, int lane) {
+  if (LINES & (1u << COG_HL_DRAW)) E.draw = hid_word<L2>(rec, COG_HL_DRAW * 32 + lane);
+  if (LINES & (1u << COG_HL_HAND)) E.hand = hid_word<L2>(rec, COG_HL_HAND * 32 + lane);
+  if (LINES & (1u << COG_HL_ACTIVE)) E.active = hid_word<L2>(rec, COG_HL_ACTIVE * 32 + lane);
+  if (LINES & (1u << COG_HL_PLAYED)) E.played = hid_word<L2>(rec, COG_HL_PLAYED * 32 + lane);
+  if (LINES & (1u << COG_HL_DISCARD)) E.discard = hid_word<L2>(rec, COG_HL_DISCARD * 32 + lane);
+  if (LINES & (1u << COG_HL_SHOP)) E.shop = hid_word<L2>(rec, COG_HL_SHOP * 32 + lane);
+  if (LINES & (1u << COG_HL_NBR)) E.nbr = hid_word<L2>(rec, COG_HL_NBR * 32 + lane);
+  if (LINES & (1u << COG_HL_PLAYER)) {
+    const int pbase = COG_HL_PLAYER * 32 + COG_PF_STRIDE * (lane & 3);
+    const uint4 p0 = hid_vec<L2>(rec, pbase), p1 = hid_vec<L2>(rec, pbase + 4);
+    E.pf = p0.x;    /* COG_PF_FLAGS */
+    E.pc = p0.y;    /* COG_PF_COUNTS */
+    E.pmv = p0.z;   /* COG_PF_MOVES */
+    E.ploc = p0.w;  /* COG_PF_LOC */
+    E.Pplay = p1.x; /* COG_PF_MPLAY */
+    E.Prem = p1.z;  /* COG_PF_MREM */
+    E.Pms = p1.w;   /* COG_PF_MMS */
+  }
+}
+enum : u32 { COG_LINES_ALL = 0xffu /* lines 0..7; the env scalars have their own loader */ };
+/* No shuffles: the seven per-lane lines are one coalesced load each; the player line and the
+ * env scalars are read as 16-byte vectors straight from the addresses every lane needs (lane l
+ * wants the fields of player l & 3 and all sixteen scalars) — same-address lanes share one
+ * transaction, so this is 6 vector loads instead of 2 loads + 27 shuffles. */
+template <bool L2 = false>
+__device__ __forceinline__ void env_load(Env &E, const u32 *rec, int lane) {
+  env_load_lines<COG_LINES_ALL, L2>(E, rec, lane);
+  env_load_scalars<L2>(E, rec, lane);
+}
+/* the same values, provably warp-uniform (a load is not, a shuffle from a fixed lane is): lets ptxas
+ * drop the divergence guards around the step logic and move scalar work to the uniform datapath */
+__device__ __forceinline__ void env_uniform_scalars_hot(Env &E) { /* what every kind of step reads */
+#ifndef COG_NO_UNIFORM_PROOF
+  E.turn = bcast(E.turn, 0); E.agent = bcast(E.agent, 0);
+  E.phase = bcast(E.phase, 0); E.n_in_market = bcast(E.n_in_market, 0);
+  E.cpf = bcast(E.cpf, 0); E.cpc = bcast(E.cpc, 0); E.info_steps = bcast(E.info_steps, 0);
+  E.Splay = bcast(E.Splay, 0); E.Srem = bcast(E.Srem, 0); E.Sms = bcast(E.Sms, 0);
+  E.res[0] = (int)bcast((u32)E.res[0], 0); E.res[1] = (int)bcast((u32)E.res[1], 0);
+  E.res[2] = (int)bcast((u32)E.res[2], 0);
+#endif
+}
+__device__ __forceinline__ void env_uniform_scalars_cold(Env &E) { /* RNG and board origin: draws, moves, resets */
+#ifndef COG_NO_UNIFORM_PROOF
+  E.rng = bcast(E.rng, 0);
+  E.minx = (int)bcast((u32)E.minx, 0); E.miny = (int)bcast((u32)E.miny, 0);
+#endif
+}
+__device__ __forceinline__ void env_uniform_scalars(Env &E) {
+  env_uniform_scalars_hot(E);
+  env_uniform_scalars_cold(E);
+}
 
-/* the mirror image: lanes 0..3 store their player's eight words, lane 0 the sixteen scalars,
- * as 16-byte vectors — no shuffles, no per-lane selection */
+__device__ __forceinline__ void env_store_scalars(const Env &E, u32 *rec, int lane, u32 pending = 0) {
+  if (lane == 0) {
+    uint4 *ev = reinterpret_cast<uint4 *>(rec + COG_HL_ENV * 32);
+    ev[0] = make_uint4(E.rng, E.turn, E.agent | (E.phase << 8) | (E.n_in_market << 16), (u32)E.res[0]);
+    ev[1] = make_uint4((u32)E.res[1], (u32)E.res[2], loc_pack(E.minx, E.miny), E.Splay);
+    ev[2] = make_uint4(0u, E.Srem, E.Sms, E.info_steps);
+    ev[3] = make_uint4(E.cpf, E.cpc, pending, 0u);
+  }
+}
 __device__ __forceinline__ void env_store(const Env &E, u32 *rec, int lane, u32 pending = 0) {
   rec[COG_HL_DRAW * 32 + lane] = E.draw;
   rec[COG_HL_HAND * 32 + lane] = E.hand;
@@ -405,13 +527,7 @@ __device__ __forceinline__ void env_store(const Env &E, u32 *rec, int lane, u32 
     pl[0] = make_uint4(E.pf, E.pc, E.pmv, E.ploc);
     pl[1] = make_uint4(E.Pplay, 0u, E.Prem, E.Pms);
   }
-  if (lane == 0) {
-    uint4 *ev = reinterpret_cast<uint4 *>(rec + COG_HL_ENV * 32);
-    ev[0] = make_uint4(E.rng, E.turn, E.agent | (E.phase << 8) | (E.n_in_market << 16), (u32)E.res[0]);
-    ev[1] = make_uint4((u32)E.res[1], (u32)E.res[2], loc_pack(E.minx, E.miny), E.Splay);
-    ev[2] = make_uint4(0u, E.Srem, E.Sms, E.info_steps);
-    ev[3] = make_uint4(E.cpf, E.cpc, pending, 0u);
-  }
+  env_store_scalars(E, rec, lane, pending);
 }
 
 /* ------------------------------------------------------------------ export */
@@ -753,7 +869,8 @@ __device__ __forceinline__ u32 movement_bits(const Env &E, int player, int r0, i
 /* ----------------------------------------------------------------- cog_env */
 /* cog_env::update_observation src/environment.cpp:252-279 */
 /* `pc` = the COG_PF_COUNTS word of player `agent` (relative byte rp) */
-__device__ __forceinline__ void env_update_observation(Env &E, int agent, int rp, u32 pc, int lane) {
+/* returns P[agent].move | P[agent].get_from_shop << 7 (also stored in lane `agent`) */
+__device__ __forceinline__ u32 env_update_observation(Env &E, int agent, int rp, u32 pc, int lane) {
   u32 move = 1u, shop = 1u;
   if (E.phase == PH_MOVEMENT) {
     const int n_active = (int)getb(pc, 1);
@@ -761,7 +878,9 @@ __device__ __forceinline__ void env_update_observation(Env &E, int agent, int rp
   } else if (E.phase == PH_BUYING) {
     shop |= shop_available_bits(E, E.res[2], lane);
   }
-  if (lane == agent) E.Pms = move | (shop << 7);
+  const u32 pms = move | (shop << 7);
+  if (lane == agent) E.Pms = pms;
+  return pms;
 }
 __device__ __forceinline__ void env_cycle_phase(Env &E) { /* include/player.h:78-84 */
   u32 n = E.phase + 1;
@@ -794,21 +913,26 @@ __device__ __forceinline__ u32 occ_index(int x, int y) { return ((u32)(x & 127) 
 
 /* Map::reset src/map.cpp:744-752 */
 __device__ __forceinline__ void bg_map_reset(BoardScratch &sc, BoardState &st, int lane) {
-  for (int w = lane; w < BG_OCC_WORDS; w += 32) sc.occ[w] = 0;
+  uint4 *o4 = reinterpret_cast<uint4 *>(sc.occ);
+  for (int w = lane; w < BG_OCC_WORDS / 4; w += 32) o4[w] = make_uint4(0u, 0u, 0u, 0u);
   st.n_list = 0;
   st.minx = st.miny = st.maxx = st.maxy = 0;
   __syncwarp();
 }
+__device__ __forceinline__ int mod6(int v) { /* v in [0, 12) */
+  return v >= 6 ? v - 6 : v;
+}
+__device__ __forceinline__ int sx8(u32 v) { return (int)(int8_t)(v & 0xffu); } /* sign-extended byte */
 
-/* Map::add_piece src/map.cpp:309-341 with MapPiece::rotate/translate :179-191.
- * Lanes place the piece's hexes in parallel.  Returns 0 or COG error (-3). */
+/* Map::add_piece src/map.cpp:309-341 with MapPiece::rotate/translate :179-191.  `rotation` is already
+ * reduced to [0, 6) (only its value mod 6 is ever observable).  Lanes 0..6 set the piece's rows in the
+ * occupancy bitmap; the bounds come from the shape's bounding box.  Returns 0 or COG error (-3). */
 __device__ __forceinline__ int bg_add_piece(BoardScratch &sc, BoardState &st, int piece, int px, int py,
                                             int rotation, int lane) {
-  const int r = rotation % 6;
   if (st.n_list >= BG_MAX_PLACED) return -3;
   /* (shared-memory reads that steer control flow go through a broadcast: provably uniform) */
-  const int rot = (int)bcast((u32)(sc.pose[piece].rot + r), 0), cx = (int)bcast((u32)(sc.pose[piece].cx + px), 0),
-            cy = (int)bcast((u32)(sc.pose[piece].cy + py), 0);
+  const int rot = mod6((int)bcast((u32)sc.pose[piece].rot, 0) + rotation),
+            cx = (int)bcast((u32)(sc.pose[piece].cx + px), 0), cy = (int)bcast((u32)(sc.pose[piece].cy + py), 0);
   __syncwarp();
   if (lane == 0) {
     sc.pose[piece].rot = (int16_t)rot;
@@ -819,23 +943,23 @@ __device__ __forceinline__ int bg_add_piece(BoardScratch &sc, BoardState &st, in
     sc.placed[st.n_list] = pl;
   }
   st.n_list++;
-  const piece_meta pm = PIECE_META[piece];
-  const xy8 *co = piece_coords(pm.size);
-  int lminx = st.minx, lminy = st.miny, lmaxx = st.maxx, lmaxy = st.maxy;
-  for (int h = lane; h < pm.n_hexes; h += 32) {
-    int x = co[h].x, y = co[h].y;
-    rotate_pt(x, y, rot);
-    x += cx;
-    y += cy;
-    const u32 b = occ_index(x, y);
-    atomicOr(&sc.occ[b >> 5], 1u << (b & 31));
-    lminx = min(lminx, x); lmaxx = max(lmaxx, x);
-    lminy = min(lminy, y); lmaxy = max(lmaxy, y);
+  const int shape = (int)PIECE_META[piece].size;
+  if (lane < 7) {
+    const u32 e = FOOT.row[shape][rot][lane];
+    const u32 bits = e >> 16;
+    const u32 X = (u32)(cx + sx8(e)) & 127u, Y = (u32)(cy + sx8(e >> 8)) & 127u;
+    const u32 w0 = Y >> 5, sh = Y & 31u;
+    /* rows of one piece are distinct x: no two lanes touch the same word */
+    if (bits) {
+      sc.occ[X * 4 + w0] |= bits << sh;
+      if (sh > 16) sc.occ[X * 4 + ((w0 + 1) & 3u)] |= bits >> (32u - sh);
+    }
   }
-  st.minx = __reduce_min_sync(COG_FULL, lminx);
-  st.miny = __reduce_min_sync(COG_FULL, lminy);
-  st.maxx = __reduce_max_sync(COG_FULL, lmaxx);
-  st.maxy = __reduce_max_sync(COG_FULL, lmaxy);
+  const u32 bb = FOOT.bbox[shape][rot];
+  st.minx = min(st.minx, cx + sx8(bb));
+  st.maxx = max(st.maxx, cx + sx8(bb >> 8));
+  st.miny = min(st.miny, cy + sx8(bb >> 16));
+  st.maxy = max(st.maxy, cy + sx8(bb >> 24));
   __syncwarp();
   /* largest cell index (coord - min + 2) / 2 must stay inside the 48 x 48 observation */
   if ((st.maxx - st.minx + 2) / 2 > COGL_GRID - 1 || (st.maxy - st.miny + 2) / 2 > COGL_GRID - 1) return -3;
@@ -843,42 +967,43 @@ __device__ __forceinline__ int bg_add_piece(BoardScratch &sc, BoardState &st, in
 }
 
 /* which connection table applies (MapPiece::get_ref_connection_points src/map.cpp:203-263):
- * returns the number of entries of host->get_centered_connections(new) (0 = none) */
+ * returns the number of entries of host->get_centered_connections(new) (0 = none).
+ * first_opt = the FIRST rotation option of the table, as a value in [0, 6) */
 __device__ __forceinline__ int bg_conn_kind(int host, int newp, int &kind, int &n_alt, int &first_opt,
                                             int &n_opts) {
   const piece_meta h = PIECE_META[host], n = PIECE_META[newp];
   kind = -1;
   if (h.size == SIZE_LARGE) {
-    if (n.size == SIZE_LARGE) { kind = 0; n_alt = 2; first_opt = -2; n_opts = 6; }
-    else if (n.size == SIZE_SMALL) { kind = 1; n_alt = 3; first_opt = -1; n_opts = 2; }
-    else if (n.size == SIZE_TRIPLE && h.type != TYPE_START) { kind = 2; n_alt = 1; first_opt = -3; n_opts = 1; }
+    if (n.size == SIZE_LARGE) { kind = 0; n_alt = 2; first_opt = 4 /* -2 */; n_opts = 6; }
+    else if (n.size == SIZE_SMALL) { kind = 1; n_alt = 3; first_opt = 5 /* -1 */; n_opts = 2; }
+    else if (n.size == SIZE_TRIPLE && h.type != TYPE_START) { kind = 2; n_alt = 1; first_opt = 3 /* -3 */; n_opts = 1; }
   } else if (h.size == SIZE_SMALL && n.size == SIZE_LARGE) {
-    kind = 3; n_alt = 6; first_opt = -2; n_opts = 6;
+    kind = 3; n_alt = 6; first_opt = 4 /* -2 */; n_opts = 6;
   }
   if (kind < 0) return 0;
   return kind == 3 ? n_alt : 7 * n_alt; /* base entries plus six rotated copies :249-260 */
 }
-/* rotation option `k` of a connection kind (:203-263): {-2..3}, {-1,2}, {-3} */
+/* rotation option `k` of a connection kind (:203-263): {-2..3}, {-1,2}, {-3}; as a value in [0, 6) */
 __device__ __forceinline__ int bg_rot_option(int kind, int k) {
-  return kind == 1 ? (k == 0 ? -1 : 2) : (kind == 2 ? -3 : k - 2);
+  return kind == 1 ? (k == 0 ? 5 : 2) : (kind == 2 ? 3 : mod6(k + 4));
 }
-/* entry e of host->get_centered_connections(new) (src/map.cpp:192-201) */
-__device__ __forceinline__ void bg_conn_entry(const BoardScratch &sc, int host, int kind, int n_alt, int e,
+/* entry e of host->get_centered_connections(new) (src/map.cpp:192-201): base point e % n_alt, rotated
+ * e / n_alt times and then by the host's own rotation — one table lookup, since rotations add up.
+ * rot_add = (e / n_alt + host rotation) mod 6 */
+__device__ __forceinline__ void bg_conn_entry(int hcx, int hcy, int hrot, int kind, int n_alt, int e,
                                               int &x, int &y, int &rot_add) {
-  const int i = e / n_alt, j = e - i * n_alt;
-  const bg_pose hp = sc.pose[host];
-  x = CONN_BASE[kind][j][0];
-  y = CONN_BASE[kind][j][1];
-  rotate_pt(x, y, i);
-  rotate_pt(x, y, hp.rot);
-  x += hp.cx;
-  y += hp.cy;
-  rot_add = i + hp.rot;
+  /* e / n_alt for n_alt in {1, 2, 3, 6} and e < 21 as a multiply-shift */
+  const u32 recip = n_alt == 1 ? 256u : (n_alt == 2 ? 128u : (n_alt == 3 ? 86u : 43u));
+  const int i = (int)(((u32)e * recip) >> 8), j = e - i * n_alt;
+  rot_add = mod6(i + hrot);
+  const u32 c = FOOT.conn[kind][j][rot_add];
+  x = sx8(c) + hcx;
+  y = sx8(c >> 8) + hcy;
 }
 
-/* Map::add_random_piece src/map.cpp:277-307 (+ overlap :53-74).  One round per host
- * piece; the lanes test that host's <= 21 connection entries in parallel against the
- * occupancy bitmap.  Returns 1 placed, 0 no candidate fits, < 0 error. */
+/* Map::add_random_piece src/map.cpp:277-307 (+ overlap :53-74).  One round per host piece; lane e
+ * tests that host's entry e (<= 21) against the occupancy bitmap: the new piece's footprint at the
+ * entry's FIRST rotation option, row by row.  Returns 1 placed, 0 no candidate fits, < 0 error. */
 __device__ __forceinline__ int bg_add_random_piece(BoardScratch &sc, BoardState &st, int piece, u32 &rng,
                                                    int lane) {
   __syncwarp();
@@ -886,29 +1011,29 @@ __device__ __forceinline__ int bg_add_random_piece(BoardScratch &sc, BoardState 
     sc.pose[piece].cx = 0; sc.pose[piece].cy = 0; sc.pose[piece].rot = 0;
   }
   __syncwarp();
-  const piece_meta pm = PIECE_META[piece];
-  const xy8 *co = piece_coords(pm.size);
+  const int shape = (int)PIECE_META[piece].size;
   u32 my_valid = 0; /* lane k keeps the valid-entry bit set of host k */
   int n_valid = 0;
   for (int k = 0; k < st.n_list; ++k) {
     const int host = (int)bcast((u32)sc.placed[k].piece, 0);
     int kind, n_alt = 1, first_opt = 0, n_opts = 0;
     const int n_ent = bg_conn_kind(host, piece, kind, n_alt, first_opt, n_opts);
-    bool ok = false;
-    if (lane < n_ent) {
-      int x, y, rot_add;
-      bg_conn_entry(sc, host, kind, n_alt, lane, x, y, rot_add);
-      const int r0 = first_opt + rot_add; /* only the FIRST rotation option is tested */
-      const rot6 m = rot_matrix(r0);
-      ok = true;
-      for (int h = 0; h < pm.n_hexes; ++h) {
-        int hx = co[h].x, hy = co[h].y;
-        rot_apply(m, hx, hy);
-        const u32 b = occ_index(hx + x, hy + y);
-        if ((sc.occ[b >> 5] >> (b & 31)) & 1u) { ok = false; break; }
-      }
+    if (!n_ent) continue;
+    const bg_pose hp = sc.pose[host];
+    const int hcx = (int)bcast((u32)hp.cx, 0), hcy = (int)bcast((u32)hp.cy, 0), hrot = (int)bcast((u32)hp.rot, 0);
+    int x, y, rot_add;
+    bg_conn_entry(hcx, hcy, hrot, kind, n_alt, lane < n_ent ? lane : 0, x, y, rot_add);
+    const u32 *rows = FOOT.row[shape][mod6(first_opt + rot_add)]; /* only the FIRST rotation option is tested */
+    u32 hit = 0;
+#pragma unroll
+    for (int j = 0; j < 7; ++j) {
+      const u32 e = rows[j];
+      const u32 X = (u32)(x + sx8(e)) & 127u, Y = (u32)(y + sx8(e >> 8)) & 127u;
+      const u32 w0 = Y >> 5;
+      const u32 window = __funnelshift_r(sc.occ[X * 4 + w0], sc.occ[X * 4 + ((w0 + 1) & 3u)], Y & 31u);
+      hit |= window & (e >> 16);
     }
-    const u32 vm = __ballot_sync(COG_FULL, ok);
+    const u32 vm = __ballot_sync(COG_FULL, lane < n_ent && !hit);
     if (lane == k) my_valid = vm;
     n_valid += __popc(vm);
   }
@@ -916,21 +1041,20 @@ __device__ __forceinline__ int bg_add_random_piece(BoardScratch &sc, BoardState 
   const u32 idx = uniform_draw(rng, (u32)n_valid);
   const u32 cnt = (u32)__popc(my_valid);
   const u32 incl = warp_incl_scan(cnt, lane);
-  const u32 hit = __ballot_sync(COG_FULL, incl > idx);
-  const int k = __ffs((int)hit) - 1;
+  const u32 hitk = __ballot_sync(COG_FULL, incl > idx);
+  const int k = __ffs((int)hitk) - 1;
   const u32 vm = bcast(my_valid, k);
   const u32 within = idx - (bcast(incl, k) - bcast(cnt, k));
-  const int e = (int)nth_set_bit(vm, within);
+  const int e = (int)nth_set_bit_warp(vm, within, lane);
   const int host = (int)bcast((u32)sc.placed[k].piece, 0);
   int kind, n_alt = 1, first_opt = 0, n_opts = 1;
   bg_conn_kind(host, piece, kind, n_alt, first_opt, n_opts);
+  const bg_pose hp = sc.pose[host];
   int x, y, rot_add;
-  bg_conn_entry(sc, host, kind, n_alt, e, x, y, rot_add);
-  x = (int)bcast((u32)x, 0);
-  y = (int)bcast((u32)y, 0);
-  rot_add = (int)bcast((u32)rot_add, 0);
+  bg_conn_entry((int)bcast((u32)hp.cx, 0), (int)bcast((u32)hp.cy, 0), (int)bcast((u32)hp.rot, 0), kind, n_alt, e, x, y,
+                rot_add);
   const int rot_idx = (int)uniform_draw(rng, (u32)n_opts);
-  const int rc = bg_add_piece(sc, st, piece, x, y, bg_rot_option(kind, rot_idx) + rot_add, lane);
+  const int rc = bg_add_piece(sc, st, piece, x, y, mod6(bg_rot_option(kind, rot_idx) + rot_add), lane);
   return rc ? rc : 1;
 }
 
@@ -1018,63 +1142,50 @@ __device__ __forceinline__ int bg_generate(BoardScratch &sc, BoardState &st, u32
   }
 }
 
-/* Map::finalize src/map.cpp:389-405 (cell index from the last add_piece :335-340).
- * (1) scatter one code per hex into the private 48 x 48 grid (pieces in placement
- * order, so later pieces win index collisions like the reference's overwrite);
- * (2) encode the 48 x 48 x 7 observation from the grid with 16-byte coalesced stores:
- * feature 1+requirement = n_required, feature 6 = is_end, feature 0 never written. */
+/* Map::finalize src/map.cpp:389-405 (cell index from the last add_piece :335-340): zero the private
+ * 48 x 48 grid and the 48 x 48 x 7 observation with 16-byte stores, then scatter, piece by piece in
+ * placement order (later pieces win index collisions like the reference's overwrite), one code per
+ * hex into the grid and the hex's seven feature bytes into the observation: feature 1 + requirement =
+ * n_required, feature 6 = is_end, feature 0 never written.  (The zero fill leaves the lines in L2, the
+ * byte stores merge there; the encode used to be a pass over all 1008 16-byte chunks of the map that
+ * re-derived every chunk from the grid — 3 100 warp instructions per reset against about 500.) */
 __device__ __forceinline__ int bg_finalize(const BoardScratch &sc, const BoardState &st, u8 *grid,
                                            u8 *mapobs, int lane) {
   uint4 *g4 = reinterpret_cast<uint4 *>(grid);
   for (int w = lane; w < COGL_GRID_BYTES / 16; w += 32) g4[w] = make_uint4(0, 0, 0, 0);
+  uint4 *m4 = reinterpret_cast<uint4 *>(mapobs);
+#pragma unroll 4
+  for (int c = lane; c < COGL_MAP_BYTES / 16; c += 32) m4[c] = make_uint4(0, 0, 0, 0);
   __syncwarp();
   bool bad = false;
   for (int k = 0; k < st.n_list; ++k) {
     const bg_placed pl = sc.placed[k];
-    const piece_meta pm = PIECE_META[pl.piece];
+    const int piece = (int)bcast((u32)pl.piece, 0), rot = (int)bcast((u32)pl.rot, 0);
+    const int ox = (int)bcast((u32)(pl.cx - st.minx + 2), 0), oy = (int)bcast((u32)(pl.cy - st.miny + 2), 0);
+    const piece_meta pm = PIECE_META[piece];
     const xy8 *co = piece_coords(pm.size);
+    const rot6 m = rot_matrix(rot);
     for (int h = lane; h < pm.n_hexes; h += 32) {
       int x = co[h].x, y = co[h].y;
-      rotate_pt(x, y, pl.rot);
-      const int ix = (x + pl.cx - st.minx + 2) / 2, iy = (y + pl.cy - st.miny + 2) / 2;
-      if (ix >= COGL_GRID || iy >= COGL_GRID) bad = true;
-      else grid[ix * COGL_GRID + iy] = PIECE_HEX[pl.piece][h];
+      rot_apply(m, x, y);
+      const int ix = (x + ox) / 2, iy = (y + oy) / 2;
+      if (ix >= COGL_GRID || iy >= COGL_GRID) {
+        bad = true;
+      } else {
+        const u32 code = PIECE_HEX[piece][h];
+        const int cell = ix * COGL_GRID + iy;
+        grid[cell] = (u8)code;
+        const u32 f = code & 7u; /* requirement + 1, 0 = none */
+        u64 v = (u64)((code >> 6) & 1u) << 48;
+        if (f) v |= (u64)((code >> 3) & 7u) << (8 * f);
+        u8 *rec = mapobs + 7 * cell;
+#pragma unroll
+        for (int b = 0; b < 7; ++b) rec[b] = (u8)(v >> (8 * b));
+      }
     }
     __syncwarp();
   }
   if (__any_sync(COG_FULL, bad)) return -3;
-  /* 16-byte chunk c covers observation bytes [16 c, 16 c + 16) = the 7-byte records of <= 4
-   * consecutive cells starting at cell0 = 16 c / 7, the first one cut off by `phase` bytes.
-   * A cell's record is one 56-bit value (byte f = feature f): n_required in byte
-   * requirement + 1, is_end in byte 6; it is shifted to its place in the 128-bit chunk. */
-  uint4 *m4 = reinterpret_cast<uint4 *>(mapobs);
-  const u32 *gw = reinterpret_cast<const u32 *>(grid);
-  for (int c = lane; c < COGL_MAP_BYTES / 16; c += 32) {
-    const int o = 16 * c, cell0 = o / 7, phase = o - 7 * cell0;
-    const int w0 = cell0 >> 2;
-    const u32 lo_w = gw[w0], hi_w = w0 + 1 < COGL_GRID_BYTES / 4 ? gw[w0 + 1] : 0u;
-    const u32 codes = __funnelshift_r(lo_w, hi_w, 8 * (cell0 & 3)); /* the 4 cells' codes */
-    u64 lo = 0, hi = 0;
-    if (codes) {
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const u32 code = (codes >> (8 * k)) & 0xffu;
-        const u32 f = code & 7u; /* requirement + 1, 0 = none */
-        u64 v = (u64)((code >> 6) & 1u) << 48;
-        if (f) v |= (u64)((code >> 3) & 7u) << (8 * f);
-        const int off = 7 * k - phase; /* byte offset of the record inside the chunk, -6 .. 21 */
-        if (off < 0) {
-          lo |= v >> (8 * -off);
-        } else if (off < 8) {
-          lo |= v << (8 * off);
-          if (off > 1) hi |= v >> (8 * (8 - off));
-        } else if (off < 16) {
-          hi |= v << (8 * (off - 8));
-        }
-      }
-    }
-    m4[c] = make_uint4((u32)lo, (u32)(lo >> 32), (u32)hi, (u32)(hi >> 32));
-  }
   return 0;
 }
 
@@ -1226,9 +1337,13 @@ __device__ __forceinline__ void env_finish_episode(Env &E, const Params &prm, co
  * is overwritten by the next step's update or by save_actionmask at the end of the turn.
  * So it is run only when a special action needs it; otherwise `obs_pending` is raised and
  * the caller runs it once after its last step. */
-template <bool LAZY, bool PLAY_ONLY>
+/* NO_END: the caller has established that this step neither ends the turn nor the episode (a card
+ * play, or a null action in the movement phase, by a player who has not won, before truncation):
+ * env_next_agent and the done check fold away.  `pms_out` (optional) receives the value
+ * update_observation computed, when it ran. */
+template <bool LAZY, bool PLAY_ONLY, bool NO_END = false>
 __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop_in, const Params &prm, const Buffers &B,
-                                        u64 i, bool &obs_pending, int lane) {
+                                        u64 i, bool &obs_pending, int lane, u32 *pms_out = nullptr) {
   /* PLAY_ONLY: the caller knows that only the `play` head can be non-zero (the sampler's
    * fast path) — every other branch of the step folds away at compile time */
   const u32 a_play = act & 0xffu;
@@ -1313,7 +1428,7 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop_in, const Pa
   }
 
   /* maybe_end_turn :244-250 */
-  const bool turn_ends = (pf & PFL_WON) || E.phase == PH_INACTIVE;
+  const bool turn_ends = !NO_END && ((pf & PFL_WON) || E.phase == PH_INACTIVE);
   if (turn_ends) {
     env_next_agent(E, pf, pc, p, prm.n_players, lane);
   } else {
@@ -1367,13 +1482,17 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop_in, const Pa
       E.pc = pc;
     }
   } else {
-    if (LAZY) obs_pending = true;
-    else env_update_observation(E, agent, 0, E.cpc, lane);
+    if (LAZY) {
+      obs_pending = true;
+    } else {
+      const u32 pms = env_update_observation(E, agent, 0, E.cpc, lane);
+      if (pms_out) *pms_out = pms;
+    }
     /* Map::player_done src/map.cpp:407-410 for the NEW current agent, or truncation.
      * The current agent can only have ARRIVED on an end hex by moving or by the turn
      * passing to a player who already stands on one */
-    bool finished = E.turn >= prm.max_steps;
-    if (turn_ends || a_move) finished = finished || hex_end(bcast(getb(E.nbr, 0), 0));
+    bool finished = !NO_END && E.turn >= prm.max_steps;
+    if (!NO_END && (turn_ends || a_move)) finished = finished || hex_end(bcast(getb(E.nbr, 0), 0));
     if (COG_UNLIKELY(finished)) {
       done = 1;
       obs_pending = false;

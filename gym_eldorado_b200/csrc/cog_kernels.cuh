@@ -16,6 +16,11 @@ enum { WARPS_PER_BLOCK = 4, BLOCK_THREADS = WARPS_PER_BLOCK * 32 };
 
 extern __shared__ uint4 cog_smem[];
 
+/* Env indices are 32-bit (a handle holds fewer than 2^32 envs; checked by cog_vec_create); the
+ * 64-bit value the address arithmetic uses is a plain zero extension, so every `i * record size`
+ * is one IMAD.WIDE.U32 instead of a 64 x 64-bit multiply. */
+__device__ __forceinline__ u64 env_index(u32 i) { return (u64)i; }
+
 __device__ __forceinline__ BoardScratch &warp_scratch() {
   return reinterpret_cast<BoardScratch *>(cog_smem)[threadIdx.x >> 5];
 }
@@ -25,7 +30,7 @@ __device__ __forceinline__ BoardScratch &warp_scratch() {
  * ActionMask is reset (include/api.h:101-103); everything else is zero. */
 __global__ void k_init(Buffers B, u64 n) {
   const int lane = threadIdx.x & 31;
-  const u64 i = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  const u64 i = env_index(blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5));
   if (i >= n) return;
   Env E;
   E.draw = E.hand = E.active = E.played = E.discard = 0;
@@ -50,7 +55,7 @@ __global__ void k_init(Buffers B, u64 n) {
  * from uint32(seed_base + i) (cog_env::reset(seed, ...) src/environment.cpp:66-77). */
 __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed) {
   const int lane = threadIdx.x & 31;
-  const u64 i = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  const u64 i = env_index(blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5));
   if (i >= n) return;
   Env E;
   env_load(E, B.hidden + i * COG_HID_WORDS, lane);
@@ -60,54 +65,138 @@ __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed)
   export_dynamic(E, B, i, 0xfu, lane, false);
 }
 
-/* vec_cog_env<N>::step(actions): one step per env from `actions` (ActionData[n], 64-byte
- * records), auto-reset included; exports only the records the step touched.  Works on the
- * envs [i0, n) (i0 a multiple of the warps per block): the host-buffer entry points run it
- * chunk by chunk so that copies and kernels of different chunks overlap.  `actions_in` may be
- * mapped pinned HOST memory (each warp pulls its 8 action bytes over PCIe itself). */
-__global__ void __launch_bounds__(BLOCK_THREADS, 8) k_step_single(Buffers B, Params prm, u64 i0, u64 n,
-                                                                  const u8 *__restrict__ actions_in, u8 *masks2) {
+/* vec_cog_env<N>::step(actions): one step per env, auto-reset included; exports only what the step
+ * changed.  SAMPLED = false: the actions come from `actions_in` (ActionData[n], 64-byte records; may be
+ * mapped pinned HOST memory — each warp pulls its 8 action bytes over PCIe itself).  SAMPLED = true
+ * (cog_vec_step_sampled): vec_action_sampler::sample(selected_action_masks) and the step in ONE
+ * kernel — the action is drawn from the env's own S mask (already in its scalar line), written to
+ * the sampler's ActionData buffer and applied; bit-identical to k_sample followed by the step.
+ * Works on the envs [i0, n) (i0 a multiple of the warps per block): the host-buffer entry points run
+ * it chunk by chunk so that copies and kernels of different chunks overlap.
+ *
+ * Two paths.  FAST: a card play, or a null action in the movement phase (78 % of the steps of the
+ * reference's own flow): the turn cannot end, so the step reads the scalar line and four per-lane
+ * lines (hand, active, shop, neighbour cache: 12 sectors instead of the record's 36), writes back the
+ * scalar line, one word each of hand / active and the agent's move / shop mask word, and exports the
+ * bytes that changed (two DeckObs bytes, two mask bytes of S, the 26 move / get_from_shop bytes of
+ * P[agent], phase + resources, steps_taken).  GENERAL: everything else — the whole record, with the
+ * episode end (rewards, Info, board generation) behind it. */
+#ifndef COG_SINGLE_BLOCKS
+#define COG_SINGLE_BLOCKS 8
+#endif
+template <bool SAMPLED>
+__global__ void __launch_bounds__(BLOCK_THREADS, COG_SINGLE_BLOCKS) k_step_single(Buffers B, Params prm, u64 i0, u64 n,
+                                                                  const u8 *__restrict__ actions_in, u8 *masks2,
+                                                                  u32 *srng, u8 *actions_out) {
   const int lane = threadIdx.x & 31;
 #ifndef COG_NO_UNIFORM_PROOF
   /* as in k_step_fused: warp index and env scalars through shuffles from a fixed lane, so that
-   * ptxas can prove them warp-uniform (BSSY 201 -> 111, BRA.DIV 68 -> 26, 6 624 -> 5 896
-   * instructions in this kernel; 76 -> 73 us per sample+step of 65 536 envs) */
-  const u64 i = i0 + (u64)blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0);
+   * ptxas can prove them warp-uniform */
+  const u64 i = env_index((u32)i0 + blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0));
 #else
-  const u64 i = i0 + (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  const u64 i = env_index((u32)i0 + blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5));
 #endif
   if (i >= n) return;
+  u32 *rec = B.hidden + i * COG_HID_WORDS;
   Env E;
-  env_load(E, B.hidden + i * COG_HID_WORDS, lane);
+  E.draw = E.played = E.discard = 0;
+  E.pf = E.pc = E.pmv = E.ploc = E.Pplay = E.Prem = E.Pms = 0;
+  /* one round trip for everything the fast path reads (and every other step reads as well): the
+   * scalar line, four per-lane lines and the action (or the sampler state) */
+  env_load_scalars(E, rec, lane);
+  enum : u32 { FAST_LINES = (1u << COG_HL_HAND) | (1u << COG_HL_ACTIVE) | (1u << COG_HL_SHOP) | (1u << COG_HL_NBR) };
+  env_load_lines<FAST_LINES>(E, rec, lane);
+  u32 act, a_shop;
+  if (SAMPLED) {
+    u32 sr = srng[i];
+    env_uniform_scalars_hot(E);
 #ifndef COG_NO_UNIFORM_PROOF
-  E.rng = bcast(E.rng, 0); E.turn = bcast(E.turn, 0); E.agent = bcast(E.agent, 0);
-  E.phase = bcast(E.phase, 0); E.n_in_market = bcast(E.n_in_market, 0);
-  E.cpf = bcast(E.cpf, 0); E.cpc = bcast(E.cpc, 0); E.info_steps = bcast(E.info_steps, 0);
-  E.Splay = bcast(E.Splay, 0); E.Srem = bcast(E.Srem, 0); E.Sms = bcast(E.Sms, 0);
-  E.res[0] = (int)bcast((u32)E.res[0], 0); E.res[1] = (int)bcast((u32)E.res[1], 0);
-  E.res[2] = (int)bcast((u32)E.res[2], 0);
-  E.minx = (int)bcast((u32)E.minx, 0); E.miny = (int)bcast((u32)E.miny, 0);
+    sr = bcast(sr, 0);
 #endif
-  /* the five ActionData bytes: every lane reads the same 8 bytes (one transaction), no shuffles */
-  const uint2 a = *reinterpret_cast<const uint2 *>(actions_in + i * COGL_ACTION_SIZE);
-  bool obs_pending = false;
-  const u32 status = env_step<false, false>(E, a.x, a.y & 0xffu, prm, B, i, obs_pending, lane);
-  if (status & 1u) {
-    env_finish_episode(E, prm, B, i, lane);
-    env_reset(E, prm, B, i, warp_scratch(), lane);
-  }
-  env_store(E, B.hidden + i * COG_HID_WORDS, lane);
-  export_dynamic(E, B, i, status >> 8, lane);
-  /* host-buffer entry point with mapped pinned memory: selected_action_masks goes straight to
-   * the caller's host array as well (92 contiguous bytes per env, posted writes over PCIe) */
-  if (masks2) export_mask(masks2 + i * COGL_MASK_SIZE, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, lane);
-  if (lane == 0) {
-    B.dones[i] = (u8)(status & 1u);
-    if ((i & (WARPS_PER_BLOCK - 1)) == 0) { /* one atomic per block */
-      const u64 left = n - i;
-      atomicAdd(&B.stats[0], (unsigned long long)(left < WARPS_PER_BLOCK ? left : WARPS_PER_BLOCK));
+    sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane);
+    __syncwarp(); /* every lane has read srng[i] before lane 0 overwrites it */
+    if (lane == 0) {
+      srng[i] = sr;
+      *reinterpret_cast<uint2 *>(actions_out + i * COGL_ACTION_SIZE) = make_uint2(act, a_shop);
     }
+  } else {
+    /* the five ActionData bytes: every lane reads the same 8 bytes (one transaction) */
+    const uint2 a = *reinterpret_cast<const uint2 *>(actions_in + i * COGL_ACTION_SIZE);
+    env_uniform_scalars_hot(E);
+#ifndef COG_NO_UNIFORM_PROOF
+    act = bcast(a.x, 0);
+    a_shop = bcast(a.y, 0) & 0xffu;
+#else
+    act = a.x;
+    a_shop = a.y & 0xffu;
+#endif
   }
+  bool obs_pending = false;
+  const u32 phase1 = E.phase == PH_INACTIVE ? (u32)PH_MOVEMENT : E.phase;
+  const bool fast = act < 256u && !a_shop && !(E.cpf & PFL_WON) && E.turn < prm.max_steps &&
+                    (act || phase1 == PH_MOVEMENT);
+  u8 *obs = B.obs + i * COGL_OBS_SIZE;
+  if (fast) {
+    const u32 Splay0 = E.Splay, Srem0 = E.Srem;
+    const int p = (int)E.agent;
+    u32 pms = 0x81u;
+    env_step<false, true, true>(E, act, 0u, prm, B, i, obs_pending, lane, &pms);
+    /* write-back: only what a play / a phase change touches */
+    u8 *pd = obs + COGL_OBS_PLAYER + COGL_PLAYER_STRIDE * p;
+    if (act && lane == (int)act) { /* Deck::activate: hand -> active of one card type */
+      rec[COG_HL_HAND * 32 + lane] = E.hand;
+      rec[COG_HL_ACTIVE * 32 + lane] = E.active;
+      pd[COGL_DK_HAND + lane - 1] = (u8)getb(E.hand, 0);
+      pd[COGL_DK_ACTIVE + lane - 1] = (u8)getb(E.active, 0);
+    }
+    if (lane == p) rec[COG_HL_PLAYER * 32 + COG_PF_STRIDE * lane + COG_PF_MMS] = pms;
+    env_store_scalars(E, rec, lane);
+    /* export */
+    if (lane == 0) {
+      *reinterpret_cast<uint4 *>(obs + COGL_OBS_PHASE) =
+          make_uint4(E.phase, __float_as_uint(0.5f * (float)E.res[0]), __float_as_uint(0.5f * (float)E.res[1]),
+                     __float_as_uint(0.5f * (float)E.res[2]));
+      (B.infos + i * COGL_INFO_SIZE)[COGL_INFO_AGENT + COGL_INFO_AGENT_STRIDE * p] = (u8)getb(E.info_steps, 0);
+      B.dones[i] = 0;
+    }
+    /* P[agent].move (7 bytes at 66) and .get_from_shop (19 bytes at 73) are 26 contiguous bools:
+     * byte 66 + k = bit k of the mask word */
+    if (lane < 26) pd[COGL_PD_MASK + COGL_AM_MOVE + lane] = (u8)((pms >> lane) & 1u);
+    /* S: a play clears at most one bit of `play` (and its play_special twin); anything else
+     * (enable_playing after a pending removal / transmission) rewrites the record */
+    const u32 d = E.Splay ^ Splay0;
+    if (COG_LIKELY(E.Srem == Srem0 && !(d & (d - 1u)))) {
+      if ((d >> lane) & 1u) {
+        const u8 bit = (u8)((E.Splay >> lane) & 1u), sbit = (u8)((spec_of(E.Splay) >> lane) & 1u);
+        u8 *m = B.masks + i * COGL_MASK_SIZE;
+        m[COGL_AM_PLAY + lane] = bit;
+        m[COGL_AM_SPECIAL + lane] = sbit;
+        if (masks2) {
+          u8 *m2 = masks2 + i * COGL_MASK_SIZE;
+          m2[COGL_AM_PLAY + lane] = bit;
+          m2[COGL_AM_SPECIAL + lane] = sbit;
+        }
+      }
+    } else {
+      export_mask(B.masks + i * COGL_MASK_SIZE, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, lane);
+      if (masks2) export_mask(masks2 + i * COGL_MASK_SIZE, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, lane);
+    }
+  } else {
+    env_load_lines<COG_LINES_ALL & ~FAST_LINES>(E, rec, lane);
+    env_uniform_scalars_cold(E);
+    const u32 status = env_step<false, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
+    if (status & 1u) {
+      env_finish_episode(E, prm, B, i, lane);
+      env_reset(E, prm, B, i, warp_scratch(), lane);
+    }
+    env_store(E, rec, lane);
+    export_dynamic(E, B, i, status >> 8, lane);
+    /* host-buffer entry point with mapped pinned memory: selected_action_masks goes straight to
+     * the caller's host array as well (92 contiguous bytes per env, posted writes over PCIe) */
+    if (masks2) export_mask(masks2 + i * COGL_MASK_SIZE, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, lane);
+    if (lane == 0) B.dones[i] = (u8)(status & 1u);
+  }
+  /* (COG_STAT_ENV_STEPS of single steps is counted by the host: n per call) */
 }
 
 /* the sampler's five action bytes of env i */
@@ -190,14 +279,15 @@ __global__ void __launch_bounds__(BLOCK_THREADS, ROLLOUT ? (MERGED ? COG_RING_BL
    * tests/test_gpu_parity.py::test_fused_equals_single_steps (12000 envs: several envs per warp,
    * episodes ending inside the launch) and tools/variant_check.py against a build with
    * -DCOG_NO_UNIFORM_PROOF. */
-  const u64 warp0 = (u64)blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0);
+  const u32 warp0 = blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0);
 #else
-  const u64 warp0 = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  const u32 warp0 = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
 #endif
-  const u64 stride = (u64)gridDim.x * WARPS_PER_BLOCK;
+  const u32 stride = gridDim.x * WARPS_PER_BLOCK;
   u64 steps_done = 0;
   u32 n_parked = 0;
-  for (u64 i = warp0; i < n; i += stride) {
+  for (u32 i32 = warp0; i32 < (u32)n; i32 += stride) {
+    const u64 i = env_index(i32);
     Env E;
     env_load(E, B.hidden + i * COG_HID_WORDS, lane);
     u32 sr = srng[i];
@@ -252,12 +342,13 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Bu
                                                                              u8 *actions_out, u32 k_steps, Rollout R) {
   const int lane = threadIdx.x & 31;
   if (*(volatile unsigned *)&B.park[0] == *(volatile unsigned *)&B.park[1]) return; /* nothing parked */
-  const u64 warp0 = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
-  const u64 stride = (u64)gridDim.x * WARPS_PER_BLOCK;
+  const u32 warp0 = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  const u32 stride = gridDim.x * WARPS_PER_BLOCK;
   BoardScratch &sc = warp_scratch();
   u64 steps_done = 0;
   u32 n_handled = 0;
-  for (u64 i = warp0; i < n; i += stride) {
+  for (u32 i32 = warp0; i32 < (u32)n; i32 += stride) {
+    const u64 i = env_index(i32);
     const u32 parked = B.hidden[i * COG_HID_WORDS + COG_HL_ENV * 32 + COG_ES_PENDING];
     if (!parked) continue;
     ++n_handled;
@@ -310,7 +401,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Bu
 /* the merged legal mask of every env's current agent as ActionMask[n] records */
 __global__ void k_merged_masks(Buffers B, u64 n, u8 *out) {
   const int lane = threadIdx.x & 31;
-  const u64 i = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  const u64 i = env_index(blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5));
   if (i >= n) return;
   Env E;
   env_load(E, B.hidden + i * COG_HID_WORDS, lane);
@@ -322,7 +413,7 @@ __global__ void k_merged_masks(Buffers B, u64 n, u8 *out) {
 /* one compact record per env for its current state; merged = which mask heads */
 __global__ void k_compact_obs(Buffers B, Params prm, u64 n, u8 *out, int merged) {
   const int lane = threadIdx.x & 31;
-  const u64 i = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  const u64 i = env_index(blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5));
   if (i >= n) return;
   Env E;
   env_load(E, B.hidden + i * COG_HID_WORDS, lane);
@@ -343,9 +434,9 @@ __global__ void k_compact_obs(Buffers B, Params prm, u64 n, u8 *out, int merged)
 __global__ void k_sample(const u8 *__restrict__ masks, u32 *srng, u8 *actions, u64 n, u8 *actions2) {
   const int lane = threadIdx.x & 31;
 #ifndef COG_NO_UNIFORM_PROOF
-  const u64 i = (u64)blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0);
+  const u64 i = env_index(blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0));
 #else
-  const u64 i = (u64)blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  const u64 i = env_index(blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5));
 #endif
   if (i >= n) return;
   const u32 *m = reinterpret_cast<const u32 *>(masks + i * COGL_MASK_SIZE);

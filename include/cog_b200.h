@@ -119,6 +119,14 @@ COG_API int cog_vec_reset_default(cog_vec *h);
  * env with auto-reset on done.  `d_actions` is a DEVICE pointer to n_envs
  * ActionData records (64 B each, 5 payload bytes). */
 COG_API int cog_vec_step(cog_vec *h, const void *d_actions);
+/* vec_action_sampler<N>::sample(envs.selected_action_masks) followed by vec_cog_env<N>::step(
+ * sampler.get_actions()) — the two calls of the reference's README / pytest / asv loop
+ * (include/vec_sampler.h:14-21, include/vec_environment.h:46-61) — as ONE kernel: the action of each env
+ * is drawn from its own selected mask, written to the sampler's ActionData buffer and applied.
+ * Bit-identical to cog_sampler_sample(s, <COG_BUF_SELECTED_MASKS>) + cog_vec_step(h, <sampler actions>),
+ * without the second launch and the mask / action round trip through memory.  (Masks from anywhere
+ * else — a policy's own array, the merged masks — go through cog_sampler_sample.) */
+COG_API int cog_vec_step_sampled(cog_vec *h, cog_sampler *s);
 /* same, but `h_actions` is a HOST pointer (what the reference's step(ndarray) gets);
  * the copy is enqueued on the handle's stream */
 COG_API int cog_vec_step_host(cog_vec *h, const void *h_actions);

@@ -43,6 +43,10 @@ class Candidate:
     def step(self):
         self.vec.step_device(self.smp.actions_ptr())
 
+    def step_sampled(self):
+        """sample(selected masks); step — one kernel (cog_vec_step_sampled)"""
+        self.vec.step_sampled(self.smp)
+
     def snapshot(self):
         v = self.vec
         return {
@@ -112,7 +116,8 @@ def first_mismatch(a, b):
 
 def run_parity(library, oracle_cls, n, seed, difficulty, max_steps, steps, regime, n_players=4,
                n_pieces=3, check_every=1, offset=0):
-    """Drive candidate and oracle side by side; returns the number of dones seen."""
+    """Drive candidate and oracle side by side; returns the number of dones seen.
+    regime "S" = regime A through the one-kernel cog_vec_step_sampled."""
     o = oracle_cls(n, seed) if offset == 0 else oracle_cls(n, seed, offset)
     c = Candidate(library, n, seed, offset)
     try:
@@ -126,6 +131,8 @@ def run_parity(library, oracle_cls, n, seed, difficulty, max_steps, steps, regim
             if regime == "A":
                 o.sample()
                 c.sample()
+            elif regime == "S":
+                o.sample()
             else:
                 if check_every != 1:
                     snap = c.snapshot()
@@ -133,9 +140,12 @@ def run_parity(library, oracle_cls, n, seed, difficulty, max_steps, steps, regim
                 o.sample(m)
                 c.sample(m)
             o.step()
-            c.step()
+            if regime == "S":
+                c.step_sampled()
+            else:
+                c.step()
             dones += int(o.dones.sum())
-            if regime != "A" or (s + 1) % check_every == 0 or s == steps - 1:
+            if regime not in ("A", "S") or (s + 1) % check_every == 0 or s == steps - 1:
                 snap = c.snapshot()
             if (s + 1) % check_every == 0 or s == steps - 1:
                 bad = first_mismatch(snap, oracle_snapshot(o))

@@ -14,6 +14,8 @@ from gym_eldorado_b200 import capi, layout
     (16, 12345, layout.MEDIUM, 30, 700, "M", 4),
     (8, 99, layout.HARD, 8, 300, "M", 2),
     (8, 99, layout.HARD, 8, 300, "A", 3),
+    (16, 5, layout.HARD, 8, 500, "S", 4),       # sample + step in one kernel (cog_vec_step_sampled)
+    (8, 6, layout.EASY, 100000, 300, "S", 2),
 ])
 def test_emulated_trajectory_parity(emu, oracle_cls, n, seed, difficulty, max_steps, steps, regime, n_players):
     parity.run_parity(emu, oracle_cls, n, seed, difficulty, max_steps, steps, regime, n_players=n_players)

@@ -29,6 +29,9 @@ def oracle_cls(gpu_oracle_cls):
     (128, 99, layout.HARD, 8, 600, "M", 2),            # BASELINE config 4 shape (2 players)
     (128, 99, layout.HARD, 8, 600, "A", 3),
     (64, 4242, layout.HARD, 8, 400, "M", 1),
+    (256, 12345, layout.EASY, 100000, 2000, "S", 4),   # configs[1] through the one-kernel sample + step
+    (1024, 4242, layout.HARD, 8, 500, "S", 4),
+    (64, 31, layout.MEDIUM, 12, 500, "S", 3),
 ])
 def test_trajectory_parity(cuda_lib, oracle_cls, n, seed, difficulty, max_steps, steps, regime, n_players):
     parity.run_parity(cuda_lib, oracle_cls, n, seed, difficulty, max_steps, steps, regime,

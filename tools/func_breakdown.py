@@ -25,8 +25,11 @@ for r in csv.reader(io.StringIO(out)):
 funcs = {}
 for name in ("cog_device.cuh", "cog_kernels.cuh"):
     fl = []
-    for i, l in enumerate(open(os.path.join(root, "gym_eldorado_b200", "csrc", name)), 1):
-        if l.startswith("__device__") or l.startswith("__global__"):
+    src_dir = os.environ.get("COG_SRC_DIR", os.path.join(root, "gym_eldorado_b200", "csrc"))  # the sources the capture was built from
+    for i, l in enumerate(open(os.path.join(src_dir, name)), 1):
+        if l.startswith("__device__") or l.startswith("__global__") or l.startswith("template <"):
+            if l.startswith("template <"):
+                continue
             m = re.search(r"(\w+)\(", l)
             if m:
                 fl.append((i, m.group(1)))
