@@ -33,6 +33,7 @@ SYMBOLS = {
     "cog_vec_step": (_int, [_vp, _vp]),
     "cog_vec_step_host": (_int, [_vp, _vp]),
     "cog_vec_step_sampled": (_int, [_vp, _vp]),
+    "cog_vec_set_autoreset": (_int, [_vp, _int]),
     "cog_vec_buffer": (_int, [_vp, _int, _P(_vp), _P(_sz), _P(_sz)]),
     "cog_vec_read": (_int, [_vp, _int, _vp, _sz]),
     "cog_vec_num_envs": (_int, [_vp, _P(_u64)]),
@@ -44,6 +45,10 @@ SYMBOLS = {
     "cog_sampler_read_actions": (_int, [_vp, _vp, _sz]),
     "cog_sampler_sample_host_io": (_int, [_vp, _vp, _vp]),
     "cog_vec_step_host_io": (_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "cog_io_path": (_int, [_vp, _vp, _P(_int), _P(_int)]),
+    "cog_sampler_sample_packed_host_io": (_int, [_vp, _vp, _vp]),
+    "cog_vec_step_packed_host_io": (_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "cog_vec_packed_masks": (_int, [_vp, _vp, _int, _int]),
     "cog_vec_run_fused": (_int, [_vp, _vp, _u64]),
     "cog_vec_run_fused_ex": (_int, [_vp, _vp, _u64, _int]),
     "cog_vec_merged_masks": (_int, [_vp, _vp]),
@@ -130,6 +135,10 @@ class VecHandle:
     def step_device(self, d_actions_ptr):
         check(self.L, self.L.cog_vec_step(self._h, d_actions_ptr))
 
+    def set_autoreset(self, on):
+        """False = single-env semantics: a finished episode keeps its terminal state, steps are ignored"""
+        check(self.L, self.L.cog_vec_set_autoreset(self._h, 1 if on else 0))
+
     def step_sampled(self, sampler):
         """sample(selected_action_masks); step(sampled actions) as one kernel."""
         check(self.L, self.L.cog_vec_step_sampled(self._h, sampler._s))
@@ -145,6 +154,30 @@ class VecHandle:
         ptr = lambda a: None if a is None else a.ctypes.data
         check(self.L, self.L.cog_vec_step_host_io(self._h, actions.ctypes.data, ptr(masks_out), ptr(rewards_out),
                                                   ptr(dones_out), ptr(agents_out)))
+
+    def io_path(self, sampler=None):
+        """(env path, sampler path) of the *_host_io entry points for pinned arrays:
+        "zero_copy", "dma_pipeline" or "measuring"."""
+        a, b = _int(-1), _int(-1)
+        check(self.L, self.L.cog_io_path(self._h, sampler._s if sampler is not None else None,
+                                         ctypes.byref(a), ctypes.byref(b)))
+        name = {1: "zero_copy", 0: "dma_pipeline", -1: "measuring"}
+        return name[a.value], name[b.value]
+
+    def step_packed_host_io(self, pactions, pmasks_out=None, rewards_out=None, dones_out=None, agents_out=None):
+        """step(packed host actions, layout.packed_action_dtype) + read-back of the packed selected masks
+        (layout.packed_mask_dtype) / rewards / dones / agent_selection into host arrays."""
+        assert pactions.dtype == layout.packed_action_dtype and pactions.flags.c_contiguous and len(pactions) == self.n
+        ptr = lambda a: None if a is None else a.ctypes.data
+        check(self.L, self.L.cog_vec_step_packed_host_io(self._h, pactions.ctypes.data, ptr(pmasks_out), ptr(rewards_out),
+                                                         ptr(dones_out), ptr(agents_out)))
+
+    def packed_masks(self, merged=False, out=None):
+        """current selected (or merged) masks in packed form as a host array"""
+        if out is None:
+            out = np.empty(self.n, dtype=layout.packed_mask_dtype)
+        check(self.L, self.L.cog_vec_packed_masks(self._h, out.ctypes.data, 1, 1 if merged else 0))
+        return out
 
     def buffer(self, which):
         """(device pointer, itemsize, count) of an exported buffer."""
@@ -242,6 +275,12 @@ class SamplerHandle:
         assert masks.dtype == layout.action_mask_dtype and masks.flags.c_contiguous and len(masks) == self.n
         assert actions_out.dtype == layout.action_dtype and actions_out.flags.c_contiguous and len(actions_out) == self.n
         check(self.L, self.L.cog_sampler_sample_host_io(self._s, masks.ctypes.data, actions_out.ctypes.data))
+
+    def sample_packed_host_io(self, pmasks, pactions_out):
+        """sample(packed host masks) with the sampled actions copied back in packed form"""
+        assert pmasks.dtype == layout.packed_mask_dtype and pmasks.flags.c_contiguous and len(pmasks) == self.n
+        assert pactions_out.dtype == layout.packed_action_dtype and len(pactions_out) == self.n
+        check(self.L, self.L.cog_sampler_sample_packed_host_io(self._s, pmasks.ctypes.data, pactions_out.ctypes.data))
 
     def actions_ptr(self):
         p = _vp()

@@ -86,7 +86,7 @@ struct cog_vec {
   cudaStream_t stream = nullptr;
   bool own_stream = false;
   cog::Buffers B{};
-  cog::Params prm{100000, 4, 3, 0}; /* cog_env::cog_env() defaults src/environment.cpp:10-15 */
+  cog::Params prm{100000, 4, 3, 0, 0}; /* cog_env::cog_env() defaults src/environment.cpp:10-15 */
   bool seeded = false;
   int sm_count = 1, fused_blocks_per_sm = 1, tail_blocks_per_sm = 1;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -100,6 +100,7 @@ struct cog_vec {
   cudaStream_t io[2] = {nullptr, nullptr}; /* copy/compute pipeline of the *_host_io entry points */
   cudaEvent_t io_ev[4] = {nullptr, nullptr, nullptr, nullptr};
   IoTune tune;
+  void *pk_actions = nullptr, *pk_masks = nullptr; /* device staging of the packed host-I/O entry points */
   uint64_t host_steps = 0;     /* env-steps of single-step calls since the last stats reset (n per call) */
 };
 
@@ -111,6 +112,7 @@ struct cog_sampler {
   uint32_t *srng = nullptr;
   uint8_t *actions = nullptr;
   void *staging = nullptr; /* device copy of host masks for cog_sampler_sample_host */
+  void *pk_masks = nullptr, *pk_actions = nullptr; /* device staging of the packed host-I/O entry points */
   cudaStream_t io[2] = {nullptr, nullptr};
   cudaEvent_t io_ev[4] = {nullptr, nullptr, nullptr, nullptr};
   IoTune tune;
@@ -223,6 +225,14 @@ uint64_t io_chunk(uint64_t n) {
 }  // namespace
 
 namespace {
+/* one launch of the single-step kernel over the envs [i0, i1) on `stream` */
+template <bool SAMPLED>
+void launch_single(cog_vec *h, cudaStream_t stream, uint64_t i0, uint64_t i1, const void *actions,
+                   uint32_t act_stride, void *masks2, void *pmasks, uint32_t *srng, uint8_t *actions_out) {
+  COG_LAUNCH(cog::k_step_single<SAMPLED>, blocks_for(i1 - i0), cog::BLOCK_THREADS, scratch_bytes(), stream, h->B, h->prm,
+             i0, i1, (const uint8_t *)actions, act_stride, (uint8_t *)masks2, (uint8_t *)pmasks, srng, actions_out);
+}
+
 template <bool MERGED, bool ROLLOUT>
 void launch_fused(cog_vec *h, cog_sampler *s, unsigned grid, unsigned tail_grid, uint32_t k_steps, const cog::Rollout &R) {
   auto hot = cog::k_step_fused<MERGED, ROLLOUT>;
@@ -314,7 +324,7 @@ int cog_vec_destroy(cog_vec *h) {
   cudaStreamSynchronize(h->stream);
   void *ptrs[] = {h->B.hidden, h->B.grid, h->B.obs, h->B.masks, h->B.rewards,
                   h->B.dones,  h->B.infos, h->B.agents, h->B.stats, h->B.err, h->B.park, h->act_staging, h->merged,
-                  h->compact, h->ring};
+                  h->compact, h->ring, h->pk_actions, h->pk_masks};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   if (h->ev0) cudaEventDestroy(h->ev0);
@@ -362,13 +372,18 @@ int cog_vec_step(cog_vec *h, const void *d_actions) {
   if (!h->seeded) return fail(COG_ERR_NOT_RESET, "step() before reset()");
   CK(cudaSetDevice(h->device));
   time_begin(h);
-  COG_LAUNCH(cog::k_step_single<false>, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B,
-             h->prm, (uint64_t)0, h->n, (const uint8_t *)d_actions, (uint8_t *)nullptr, (uint32_t *)nullptr,
-             (uint8_t *)nullptr);
+  launch_single<false>(h, h->stream, 0, h->n, d_actions, COG_ACTION_SIZE, nullptr, nullptr, nullptr, nullptr);
   time_end(h);
   h->host_steps += h->n;
   g_launches++;
   CK(cudaGetLastError());
+  return COG_OK;
+}
+
+int cog_vec_set_autoreset(cog_vec *h, int on) {
+  if (!h) return fail(COG_ERR_INVALID, "NULL handle");
+  if (on) h->prm.flags &= ~(uint32_t)cog::COG_PRM_NO_AUTORESET;
+  else h->prm.flags |= (uint32_t)cog::COG_PRM_NO_AUTORESET;
   return COG_OK;
 }
 
@@ -379,8 +394,7 @@ int cog_vec_step_sampled(cog_vec *h, cog_sampler *s) {
   CK(cudaSetDevice(h->device));
   if (s->stream != h->stream) CK(cudaStreamSynchronize(s->stream));
   time_begin(h);
-  COG_LAUNCH(cog::k_step_single<true>, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B,
-             h->prm, (uint64_t)0, h->n, (const uint8_t *)nullptr, (uint8_t *)nullptr, s->srng, s->actions);
+  launch_single<true>(h, h->stream, 0, h->n, nullptr, COG_ACTION_SIZE, nullptr, nullptr, s->srng, s->actions);
   time_end(h);
   h->host_steps += h->n;
   g_launches++;
@@ -475,6 +489,8 @@ int cog_sampler_destroy(cog_sampler *s) {
   if (s->srng) cudaFree(s->srng);
   if (s->actions) cudaFree(s->actions);
   if (s->staging) cudaFree(s->staging);
+  if (s->pk_masks) cudaFree(s->pk_masks);
+  if (s->pk_actions) cudaFree(s->pk_actions);
   for (cudaStream_t st : s->io)
     if (st) cudaStreamDestroy(st);
   for (cudaEvent_t e : s->io_ev)
@@ -487,7 +503,7 @@ int cog_sampler_destroy(cog_sampler *s) {
 int cog_sampler_sample(cog_sampler *s, const void *d_masks) {
   if (!s || !d_masks) return fail(COG_ERR_INVALID, "NULL argument");
   CK(cudaSetDevice(s->device));
-  COG_LAUNCH(cog::k_sample, blocks_for(s->n), cog::BLOCK_THREADS, 0, s->stream, (const uint8_t *)d_masks,
+  COG_LAUNCH(cog::k_sample<false>, blocks_for(s->n), cog::BLOCK_THREADS, 0, s->stream, (const uint8_t *)d_masks,
              s->srng, s->actions, s->n, (uint8_t *)nullptr);
   g_launches++;
   CK(cudaGetLastError());
@@ -534,7 +550,7 @@ int cog_sampler_sample_host_io(cog_sampler *s, const void *h_masks, void *h_acti
   const bool measuring = eligible && forced < 0 && s->tune.choice < 0;
   const double t0 = measuring ? now_seconds() : 0.0;
   if (eligible && (forced == 1 || s->tune.use_zero())) {
-    COG_LAUNCH(cog::k_sample, blocks_for(s->n), cog::BLOCK_THREADS, 0, s->stream, (const uint8_t *)zm, s->srng,
+    COG_LAUNCH(cog::k_sample<false>, blocks_for(s->n), cog::BLOCK_THREADS, 0, s->stream, (const uint8_t *)zm, s->srng,
                s->actions, s->n, (uint8_t *)za);
     g_launches++;
     CK(cudaGetLastError());
@@ -553,7 +569,7 @@ int cog_sampler_sample_host_io(cog_sampler *s, const void *h_masks, void *h_acti
       uint8_t *d_a = s->actions + i0 * COG_ACTION_SIZE;
       CK(cudaMemcpyAsync(d_m, (const uint8_t *)h_masks + i0 * COG_MASK_SIZE, cnt * COG_MASK_SIZE,
                          cudaMemcpyHostToDevice, io[k]));
-      COG_LAUNCH(cog::k_sample, blocks_for(cnt), cog::BLOCK_THREADS, 0, io[k], d_m, s->srng + i0, d_a, cnt,
+      COG_LAUNCH(cog::k_sample<false>, blocks_for(cnt), cog::BLOCK_THREADS, 0, io[k], d_m, s->srng + i0, d_a, cnt,
                  (uint8_t *)nullptr);
       CK(cudaMemcpyAsync((uint8_t *)h_actions_out + i0 * COG_ACTION_SIZE, d_a, cnt * COG_ACTION_SIZE,
                          cudaMemcpyDeviceToHost, io[k]));
@@ -576,8 +592,7 @@ int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, v
   const bool measuring = eligible && forced < 0 && h->tune.choice < 0;
   const double t0 = measuring ? now_seconds() : 0.0;
   if (eligible && (forced == 1 || h->tune.use_zero())) {
-    COG_LAUNCH(cog::k_step_single<false>, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm,
-               (uint64_t)0, h->n, (const uint8_t *)za, (uint8_t *)zm, (uint32_t *)nullptr, (uint8_t *)nullptr);
+    launch_single<false>(h, h->stream, 0, h->n, za, COG_ACTION_SIZE, zm, nullptr, nullptr, nullptr);
     h->host_steps += h->n;
     g_launches++;
     CK(cudaGetLastError());
@@ -601,8 +616,7 @@ int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, v
       CK(cudaMemcpyAsync((uint8_t *)h->act_staging + i0 * COG_ACTION_SIZE,
                          (const uint8_t *)h_actions + i0 * COG_ACTION_SIZE, cnt * COG_ACTION_SIZE,
                          cudaMemcpyHostToDevice, st));
-      COG_LAUNCH(cog::k_step_single<false>, blocks_for(cnt), cog::BLOCK_THREADS, scratch_bytes(), st, h->B, h->prm, i0,
-                 i0 + cnt, (const uint8_t *)h->act_staging, (uint8_t *)nullptr, (uint32_t *)nullptr, (uint8_t *)nullptr);
+      launch_single<false>(h, st, i0, i0 + cnt, h->act_staging, COG_ACTION_SIZE, nullptr, nullptr, nullptr, nullptr);
       if (h_masks_out)
         CK(cudaMemcpyAsync((uint8_t *)h_masks_out + i0 * COG_MASK_SIZE, h->B.masks + i0 * COG_MASK_SIZE,
                            cnt * COG_MASK_SIZE, cudaMemcpyDeviceToHost, st));
@@ -620,6 +634,74 @@ int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, v
   if (!rc) h->host_steps += h->n;
   if (measuring && !rc) h->tune.record(false, now_seconds() - t0);
   return rc;
+}
+
+/* ---- packed host I/O: 16-byte masks, 8-byte actions; staged through device memory by DMA (a 65 536-env
+ * batch is 1 MB of masks and 0.5 MB of actions: two short copies beat 65 536 small PCIe reads) ---- */
+int cog_sampler_sample_packed_host_io(cog_sampler *s, const void *h_pmasks, void *h_pactions_out) {
+  if (!s || !h_pmasks || !h_pactions_out) return fail(COG_ERR_INVALID, "NULL argument");
+  CK(cudaSetDevice(s->device));
+  if (!s->pk_masks) CK(cudaMalloc(&s->pk_masks, s->n * COGL_PACKED_MASK_SIZE));
+  if (!s->pk_actions) CK(cudaMalloc(&s->pk_actions, s->n * COGL_PACKED_ACTION_SIZE));
+  CK(cudaMemcpyAsync(s->pk_masks, h_pmasks, s->n * COGL_PACKED_MASK_SIZE, cudaMemcpyHostToDevice, s->stream));
+  COG_LAUNCH(cog::k_sample<true>, blocks_for(s->n), cog::BLOCK_THREADS, 0, s->stream, (const uint8_t *)s->pk_masks,
+             s->srng, s->actions, s->n, (uint8_t *)s->pk_actions);
+  g_launches++;
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(h_pactions_out, s->pk_actions, s->n * COGL_PACKED_ACTION_SIZE, cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream)); /* the host array is complete on return */
+  return COG_OK;
+}
+
+int cog_vec_step_packed_host_io(cog_vec *h, const void *h_pactions, void *h_pmasks_out, void *h_rewards_out,
+                                void *h_dones_out, void *h_agents_out) {
+  if (!h || !h_pactions) return fail(COG_ERR_INVALID, "NULL argument");
+  if (!h->seeded) return fail(COG_ERR_NOT_RESET, "step() before reset()");
+  CK(cudaSetDevice(h->device));
+  if (!h->pk_actions) CK(cudaMalloc(&h->pk_actions, h->n * COGL_PACKED_ACTION_SIZE));
+  if (!h->pk_masks) CK(cudaMalloc(&h->pk_masks, h->n * COGL_PACKED_MASK_SIZE));
+  CK(cudaMemcpyAsync(h->pk_actions, h_pactions, h->n * COGL_PACKED_ACTION_SIZE, cudaMemcpyHostToDevice, h->stream));
+  time_begin(h);
+  launch_single<false>(h, h->stream, 0, h->n, h->pk_actions, COGL_PACKED_ACTION_SIZE, nullptr,
+                       h_pmasks_out ? h->pk_masks : nullptr, nullptr, nullptr);
+  time_end(h);
+  h->host_steps += h->n;
+  g_launches++;
+  CK(cudaGetLastError());
+  if (h_pmasks_out)
+    CK(cudaMemcpyAsync(h_pmasks_out, h->pk_masks, h->n * COGL_PACKED_MASK_SIZE, cudaMemcpyDeviceToHost, h->stream));
+  if (h_dones_out) CK(cudaMemcpyAsync(h_dones_out, h->B.dones, h->n, cudaMemcpyDeviceToHost, h->stream));
+  if (h_agents_out) CK(cudaMemcpyAsync(h_agents_out, h->B.agents, h->n, cudaMemcpyDeviceToHost, h->stream));
+  if (h_rewards_out) CK(cudaMemcpyAsync(h_rewards_out, h->B.rewards, h->n * 16, cudaMemcpyDeviceToHost, h->stream));
+  return check_device_error(h); /* synchronises: the host arrays are complete on return */
+}
+
+int cog_vec_packed_masks(cog_vec *h, void *dst, int dst_is_host, int mask_mode) {
+  if (!h || !dst) return fail(COG_ERR_INVALID, "NULL argument");
+  if (mask_mode != COG_MASKS_SELECTED && mask_mode != COG_MASKS_MERGED) return fail(COG_ERR_INVALID, "unknown mask mode");
+  if (!h->seeded) return fail(COG_ERR_NOT_RESET, "masks before reset()");
+  CK(cudaSetDevice(h->device));
+  void *d = dst;
+  if (dst_is_host) {
+    if (!h->pk_masks) CK(cudaMalloc(&h->pk_masks, h->n * COGL_PACKED_MASK_SIZE));
+    d = h->pk_masks;
+  }
+  COG_LAUNCH(cog::k_packed_masks, blocks_for(h->n), cog::BLOCK_THREADS, 0, h->stream, h->B, h->n, (uint8_t *)d,
+             mask_mode == COG_MASKS_MERGED ? 1 : 0);
+  g_launches++;
+  CK(cudaGetLastError());
+  if (dst_is_host) {
+    CK(cudaMemcpyAsync(dst, d, h->n * COGL_PACKED_MASK_SIZE, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
+  return COG_OK;
+}
+
+int cog_io_path(cog_vec *h, cog_sampler *s, int *vec_path, int *sampler_path) {
+  const int forced = io_forced();
+  if (vec_path) *vec_path = !h ? -1 : forced >= 0 ? forced : h->tune.choice;
+  if (sampler_path) *sampler_path = !s ? -1 : forced >= 0 ? forced : s->tune.choice;
+  return COG_OK;
 }
 
 int cog_vec_run_fused(cog_vec *h, cog_sampler *s, uint64_t k_steps) {
@@ -693,6 +775,8 @@ int cog_vec_run_fused_ex(cog_vec *h, cog_sampler *s, uint64_t k_steps, int mask_
   if (s->n != h->n || s->device != h->device) return fail(COG_ERR_INVALID, "sampler and envs differ in size or device");
   if (!h->seeded) return fail(COG_ERR_NOT_RESET, "run() before reset()");
   if (k_steps > 0xffffffffull) return fail(COG_ERR_INVALID, "k_steps must fit 32 bits");
+  if (h->prm.flags & cog::COG_PRM_NO_AUTORESET)
+    return fail(COG_ERR_INVALID, "the fused loop needs auto-reset (cog_vec_set_autoreset(h, 1))");
   CK(cudaSetDevice(h->device));
   if (s->stream != h->stream) CK(cudaStreamSynchronize(s->stream));
   /* persistent grid: every SM filled once, warps walk the envs with a grid stride */

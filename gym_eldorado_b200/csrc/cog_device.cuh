@@ -343,7 +343,12 @@ __device__ __forceinline__ void rotate_pt(int &x, int &y, int times) { rot_apply
 struct Params {
   u32 max_steps;
   u32 n_players, n_pieces, difficulty;
+  u32 flags; /* COG_PRM_* */
 };
+/* single-env semantics (cog_env::step, src/environment.cpp:91-95,187-207): a finished episode is NOT
+ * reset by the step that ends it; the env keeps its terminal state and ignores further steps
+ * (dead_step) until reset() */
+enum { COG_PRM_NO_AUTORESET = 1 };
 
 /* device buffers of one handle */
 struct Buffers {
@@ -505,16 +510,16 @@ __device__ __forceinline__ void env_uniform_scalars(Env &E) {
   env_uniform_scalars_cold(E);
 }
 
-__device__ __forceinline__ void env_store_scalars(const Env &E, u32 *rec, int lane, u32 pending = 0) {
+__device__ __forceinline__ void env_store_scalars(const Env &E, u32 *rec, int lane, u32 pending = 0, u32 dead = 0) {
   if (lane == 0) {
     uint4 *ev = reinterpret_cast<uint4 *>(rec + COG_HL_ENV * 32);
     ev[0] = make_uint4(E.rng, E.turn, E.agent | (E.phase << 8) | (E.n_in_market << 16), (u32)E.res[0]);
     ev[1] = make_uint4((u32)E.res[1], (u32)E.res[2], loc_pack(E.minx, E.miny), E.Splay);
     ev[2] = make_uint4(0u, E.Srem, E.Sms, E.info_steps);
-    ev[3] = make_uint4(E.cpf, E.cpc, pending, 0u);
+    ev[3] = make_uint4(E.cpf, E.cpc, pending, dead);
   }
 }
-__device__ __forceinline__ void env_store(const Env &E, u32 *rec, int lane, u32 pending = 0) {
+__device__ __forceinline__ void env_store(const Env &E, u32 *rec, int lane, u32 pending = 0, u32 dead = 0) {
   rec[COG_HL_DRAW * 32 + lane] = E.draw;
   rec[COG_HL_HAND * 32 + lane] = E.hand;
   rec[COG_HL_ACTIVE * 32 + lane] = E.active;
@@ -527,7 +532,7 @@ __device__ __forceinline__ void env_store(const Env &E, u32 *rec, int lane, u32 
     pl[0] = make_uint4(E.pf, E.pc, E.pmv, E.ploc);
     pl[1] = make_uint4(E.Pplay, 0u, E.Prem, E.Pms);
   }
-  env_store_scalars(E, rec, lane, pending);
+  env_store_scalars(E, rec, lane, pending, dead);
 }
 
 /* ------------------------------------------------------------------ export */
@@ -1198,6 +1203,14 @@ __device__ __forceinline__ void env_to_absolute(Env &E, int lane) {
   E.agent = 0;
   E.cpf = bcast(E.pf, 0);
   E.cpc = bcast(E.pc, 0);
+}
+
+/* the inverse: from absolute order (agent 0) back to the rotated order of agent `a` */
+__device__ __forceinline__ void env_from_absolute(Env &E, u32 a, int lane) {
+  env_rotate(E, a);
+  E.agent = a;
+  E.cpf = bcast(E.pf, (int)a);
+  E.cpc = bcast(E.pc, (int)a);
 }
 
 __device__ __forceinline__ void report_error(const Buffers &B, int code, u64 i, int lane) {

@@ -82,12 +82,24 @@ __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed)
  * P[agent], phase + resources, steps_taken).  GENERAL: everything else — the whole record, with the
  * episode end (rewards, Info, board generation) behind it. */
 #ifndef COG_SINGLE_BLOCKS
-#define COG_SINGLE_BLOCKS 8
+#define COG_SINGLE_BLOCKS 10 /* measured: 8 blocks 43.3 us, 10 blocks 38.3 us, 12 blocks 41.3 us (spills) per sampled step of 65 536 envs */
 #endif
+/* act_stride: bytes between the action records of consecutive envs in `actions_in` — COGL_ACTION_SIZE
+ * for ActionData[n], COGL_PACKED_ACTION_SIZE for the packed form (the same five bytes + 3 of padding).
+ * pmasks (optional): selected_action_masks in packed form (COGL_PACKED_MASK_SIZE bytes per env: the four
+ * heads as bit sets), for the packed host-I/O entry points. */
+template <bool SAMPLED>
+__device__ __forceinline__ void step_one_env(const Buffers &B, const Params &prm, u64 i, const u8 *__restrict__ actions_in,
+                                             u32 act_stride, u8 *masks2, u8 *pmasks, u32 *srng, u8 *actions_out, int lane);
+
+/* One warp per env; the hardware block scheduler hands out the envs four at a time.  (Tried and dropped: a
+ * resident grid whose warps draw env indices from a device counter, the next index fetched while the
+ * current env is stepped — 65 536 atomics on one address per launch serialise in L2: 66 us per step of
+ * 65 536 envs against 40 us, gpurun_out/r02_d_api_loop.txt.) */
 template <bool SAMPLED>
 __global__ void __launch_bounds__(BLOCK_THREADS, COG_SINGLE_BLOCKS) k_step_single(Buffers B, Params prm, u64 i0, u64 n,
-                                                                  const u8 *__restrict__ actions_in, u8 *masks2,
-                                                                  u32 *srng, u8 *actions_out) {
+                                                                  const u8 *__restrict__ actions_in, u32 act_stride,
+                                                                  u8 *masks2, u8 *pmasks, u32 *srng, u8 *actions_out) {
   const int lane = threadIdx.x & 31;
 #ifndef COG_NO_UNIFORM_PROOF
   /* as in k_step_fused: warp index and env scalars through shuffles from a fixed lane, so that
@@ -97,7 +109,15 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_SINGLE_BLOCKS) k_step_singl
   const u64 i = env_index((u32)i0 + blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5));
 #endif
   if (i >= n) return;
+  step_one_env<SAMPLED>(B, prm, i, actions_in, act_stride, masks2, pmasks, srng, actions_out, lane);
+}
+
+template <bool SAMPLED>
+__device__ __forceinline__ void step_one_env(const Buffers &B, const Params &prm, u64 i, const u8 *__restrict__ actions_in,
+                                             u32 act_stride, u8 *masks2, u8 *pmasks, u32 *srng, u8 *actions_out, int lane) {
   u32 *rec = B.hidden + i * COG_HID_WORDS;
+  if (COG_UNLIKELY(prm.flags & COG_PRM_NO_AUTORESET)) /* dead_step src/environment.cpp:92-95 */
+    if (bcast(rec[COG_HL_ENV * 32 + COG_ES_DEAD], 0)) return;
   Env E;
   E.draw = E.played = E.discard = 0;
   E.pf = E.pc = E.pmv = E.ploc = E.Pplay = E.Prem = E.Pms = 0;
@@ -121,7 +141,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_SINGLE_BLOCKS) k_step_singl
     }
   } else {
     /* the five ActionData bytes: every lane reads the same 8 bytes (one transaction) */
-    const uint2 a = *reinterpret_cast<const uint2 *>(actions_in + i * COGL_ACTION_SIZE);
+    const uint2 a = *reinterpret_cast<const uint2 *>(actions_in + i * act_stride);
     env_uniform_scalars_hot(E);
 #ifndef COG_NO_UNIFORM_PROOF
     act = bcast(a.x, 0);
@@ -185,17 +205,26 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_SINGLE_BLOCKS) k_step_singl
     env_load_lines<COG_LINES_ALL & ~FAST_LINES>(E, rec, lane);
     env_uniform_scalars_cold(E);
     const u32 status = env_step<false, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
+    u32 dead = 0;
     if (status & 1u) {
+      const u32 agent = E.agent;
       env_finish_episode(E, prm, B, i, lane);
-      env_reset(E, prm, B, i, warp_scratch(), lane);
+      if (COG_UNLIKELY(prm.flags & COG_PRM_NO_AUTORESET)) {
+        env_from_absolute(E, agent, lane); /* the terminal state stays (cog_env::step does not reset) */
+        dead = 1;
+      } else {
+        env_reset(E, prm, B, i, warp_scratch(), lane);
+      }
     }
-    env_store(E, rec, lane);
+    env_store(E, rec, lane, 0, dead);
     export_dynamic(E, B, i, status >> 8, lane);
     /* host-buffer entry point with mapped pinned memory: selected_action_masks goes straight to
      * the caller's host array as well (92 contiguous bytes per env, posted writes over PCIe) */
     if (masks2) export_mask(masks2 + i * COGL_MASK_SIZE, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, lane);
     if (lane == 0) B.dones[i] = (u8)(status & 1u);
   }
+  if (pmasks && lane == 0)
+    *reinterpret_cast<uint4 *>(pmasks + i * COGL_PACKED_MASK_SIZE) = make_uint4(E.Splay, E.Srem, E.Sms, spec_of(E.Splay));
   /* (COG_STAT_ENV_STEPS of single steps is counted by the host: n per call) */
 }
 
@@ -410,6 +439,19 @@ __global__ void k_merged_masks(Buffers B, u64 n, u8 *out) {
   export_mask(out + i * COGL_MASK_SIZE, E.Splay, spec_of(E.Splay), rem, ms, lane);
 }
 
+/* selected_action_masks (merged = 0) or the merged legal mask (merged = 1) of every env in packed form */
+__global__ void k_packed_masks(Buffers B, u64 n, u8 *out, int merged) {
+  const int lane = threadIdx.x & 31;
+  const u64 i = env_index(blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5));
+  if (i >= n) return;
+  Env E;
+  env_load(E, B.hidden + i * COG_HID_WORDS, lane);
+  u32 rem = E.Srem, ms = E.Sms;
+  if (merged) merged_heads(E, lane, rem, ms);
+  if (lane == 0)
+    *reinterpret_cast<uint4 *>(out + i * COGL_PACKED_MASK_SIZE) = make_uint4(E.Splay, rem, ms, spec_of(E.Splay));
+}
+
 /* one compact record per env for its current state; merged = which mask heads */
 __global__ void k_compact_obs(Buffers B, Params prm, u64 n, u8 *out, int merged) {
   const int lane = threadIdx.x & 31;
@@ -431,6 +473,9 @@ __global__ void k_compact_obs(Buffers B, Params prm, u64 n, u8 *out, int merged)
  * PCIe); lane k then fetches bool k of each head from the lane that holds its word, and a
  * ballot turns the head into a bit set.  actions2 (optional): a second destination for the
  * ActionData bytes, e.g. the caller's mapped host array. */
+/* PACKED: `masks` holds COGL_PACKED_MASK_SIZE bytes per env (the heads as bit sets, see cog_b200.h) and
+ * actions2 gets COGL_PACKED_ACTION_SIZE bytes per env. */
+template <bool PACKED>
 __global__ void k_sample(const u8 *__restrict__ masks, u32 *srng, u8 *actions, u64 n, u8 *actions2) {
   const int lane = threadIdx.x & 31;
 #ifndef COG_NO_UNIFORM_PROOF
@@ -439,13 +484,28 @@ __global__ void k_sample(const u8 *__restrict__ masks, u32 *srng, u8 *actions, u
   const u64 i = env_index(blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5));
 #endif
   if (i >= n) return;
-  const u32 *m = reinterpret_cast<const u32 *>(masks + i * COGL_MASK_SIZE);
-  const u32 w = lane < 23 ? m[lane] : 0u;
 #ifndef COG_NO_UNIFORM_PROOF
   u32 sr = bcast(srng[i], 0);
 #else
   u32 sr = srng[i];
 #endif
+  u32 act, a_shop;
+  if (PACKED) {
+    const uint4 pm = *reinterpret_cast<const uint4 *>(masks + i * COGL_PACKED_MASK_SIZE);
+    /* (a caller's array: keep the heads inside their ranges, like the ballots of the bool form do) */
+    const u32 play = bcast(pm.x, 0) & 0x3fffffu, rem = bcast(pm.y, 0) & 0x3fffffu, ms = bcast(pm.z, 0) & 0x3ffffffu,
+              spec = bcast(pm.w, 0) & 0x3fffffu;
+    sample_action(sr, play, spec, rem, ms, act, a_shop, lane);
+    __syncwarp();
+    if (lane == 0) {
+      srng[i] = sr;
+      *reinterpret_cast<uint2 *>(actions + i * COGL_ACTION_SIZE) = make_uint2(act, a_shop);
+      if (actions2) *reinterpret_cast<uint2 *>(actions2 + i * COGL_PACKED_ACTION_SIZE) = make_uint2(act, a_shop);
+    }
+    return;
+  }
+  const u32 *m = reinterpret_cast<const u32 *>(masks + i * COGL_MASK_SIZE);
+  const u32 w = lane < 23 ? m[lane] : 0u;
   /* bool (base + lane) of the record = byte ((base + lane) & 3) of word (base + lane) >> 2 */
 #define COG_HEAD(base, count) \
   __ballot_sync(COG_FULL, ((__shfl_sync(COG_FULL, w, ((base) + lane) >> 2) >> (8 * (((base) + lane) & 3))) & 0xffu) && \
@@ -456,7 +516,6 @@ __global__ void k_sample(const u8 *__restrict__ masks, u32 *srng, u8 *actions, u
   const u32 move = COG_HEAD(COGL_AM_MOVE, 7);
   const u32 shop = COG_HEAD(COGL_AM_SHOP, 19);
 #undef COG_HEAD
-  u32 act, a_shop;
   sample_action(sr, play, spec, rem, move | (shop << 7), act, a_shop, lane);
   __syncwarp(); /* every lane has read srng[i] before lane 0 overwrites it */
   if (lane == 0) {

@@ -29,7 +29,12 @@ enum {
   COGL_INFO_SIZE = 192,
   COGL_INFO_AGENT = 4, COGL_INFO_AGENT_STRIDE = 32,
   COGL_GRID = 48,
-  COGL_GRID_BYTES = 48 * 48
+  COGL_GRID_BYTES = 48 * 48,
+  /* packed host-I/O records (not in the reference; include/cog_b200.h): an ActionMask as four bit sets —
+   * u32 play, u32 remove, u32 move | get_from_shop << 7, u32 play_special (the mask words of the compact
+   * record) — and the five ActionData bytes in an 8-byte record */
+  COGL_PACKED_MASK_SIZE = 16,
+  COGL_PACKED_ACTION_SIZE = 8
 };
 
 /* ---- hidden per-env record ------------------------------------------------
@@ -72,9 +77,11 @@ enum {
   COG_ES_INFOSTEPS = 11, /* Info.agent_infos[k].steps_taken, one byte per player (rotated) */
   COG_ES_CPF = 12, COG_ES_CPC = 13, /* live COG_PF_FLAGS / COG_PF_COUNTS of the current agent
                                        (that player's words in line 7 are stale) */
-  COG_ES_PENDING = 14 /* only non-zero INSIDE a fused launch: 1 + the sample+step iterations this env
-                         still owes after an episode end (phase 2 of k_step<true> resets the env,
-                         runs them and clears the word) */
+  COG_ES_PENDING = 14, /* only non-zero INSIDE a fused launch: 1 + the sample+step iterations this env
+                          still owes after an episode end (k_step_tail resets the env, runs them and
+                          clears the word) */
+  COG_ES_DEAD = 15     /* single-env semantics only (auto-reset off): the episode is over, steps are
+                          ignored until reset() */
 };
 
 /* ------------------------------------------------------------------------------------------

@@ -109,6 +109,45 @@ compact_dtype = np.dtype({
 })
 GRID_BYTES = GRIDSIZE * GRIDSIZE
 
+# Not in the reference: the packed host-I/O records (include/cog_b200.h, cog_*_packed_host_io):
+# an ActionMask as four bit sets (bit k of a word = bool k of the head) and the five ActionData
+# bytes in eight.
+packed_mask_dtype = np.dtype({
+    "names": ["play", "remove", "move_shop", "play_special"],
+    "formats": [np.uint32] * 4, "offsets": [0, 4, 8, 12], "itemsize": 16,
+})
+packed_action_dtype = np.dtype({
+    "names": ["play", "play_special", "remove", "move", "get_from_shop"],
+    "formats": [np.uint8] * 5, "offsets": [0, 1, 2, 3, 4], "itemsize": 8,
+})
+
+
+def _bits(a):
+    a = np.asarray(a).astype(np.uint64)
+    return (a << np.arange(a.shape[1], dtype=np.uint64)).sum(axis=1).astype(np.uint32)
+
+
+def pack_masks(masks):
+    """ActionMask[n] (bool per byte) -> packed_mask_dtype[n]"""
+    out = np.zeros(len(masks), dtype=packed_mask_dtype)
+    out["play"] = _bits(masks["play"])
+    out["remove"] = _bits(masks["remove"])
+    out["move_shop"] = _bits(masks["move"]) | (_bits(masks["get_from_shop"]) << np.uint32(7))
+    out["play_special"] = _bits(masks["play_special"])
+    return out
+
+
+def unpack_masks(packed):
+    """packed_mask_dtype[n] -> ActionMask[n]"""
+    out = np.zeros(len(packed), dtype=action_mask_dtype)
+    bit = lambda w, n, sh=0: ((w[:, None] >> (np.arange(n, dtype=np.uint32) + np.uint32(sh))) & 1).astype(np.bool_)
+    out["play"] = bit(packed["play"], N_CARDTYPES + 1)
+    out["remove"] = bit(packed["remove"], N_CARDTYPES + 1)
+    out["play_special"] = bit(packed["play_special"], N_CARDTYPES + 1)
+    out["move"] = bit(packed["move_shop"], N_DIRECTIONS)
+    out["get_from_shop"] = bit(packed["move_shop"], N_BUYABLETYPES + 1, 7)
+    return out
+
 
 def grid_to_map(grid):
     """uint8[..., 48*48] hex codes (BUF_GRID) -> uint8[..., 48, 48, 7] map observation

@@ -119,6 +119,12 @@ COG_API int cog_vec_reset_default(cog_vec *h);
  * env with auto-reset on done.  `d_actions` is a DEVICE pointer to n_envs
  * ActionData records (64 B each, 5 payload bytes). */
 COG_API int cog_vec_step(cog_vec *h, const void *d_actions);
+/* Auto-reset off = the semantics of the reference's SINGLE env (cog_env::step, src/environment.cpp:91-95,
+ * 187-207, bound at src/pybind/single_env.cpp:13-32): the step that ends an episode writes rewards / Info
+ * and sets done, but does not reset; the env keeps its terminal state and ignores further steps until
+ * cog_vec_reset(_default).  On (the default) = vec_cog_env<N>::step_single (include/vec_environment.h:53-61).
+ * The fused loop requires auto-reset. */
+COG_API int cog_vec_set_autoreset(cog_vec *h, int on);
 /* vec_action_sampler<N>::sample(envs.selected_action_masks) followed by vec_cog_env<N>::step(
  * sampler.get_actions()) — the two calls of the reference's README / pytest / asv loop
  * (include/vec_sampler.h:14-21, include/vec_environment.h:46-61) — as ONE kernel: the action of each env
@@ -171,6 +177,32 @@ COG_API int cog_sampler_read_actions(cog_sampler *s, void *h_dst, size_t nbytes)
 COG_API int cog_sampler_sample_host_io(cog_sampler *s, const void *h_masks, void *h_actions_out);
 COG_API int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, void *h_rewards_out,
                                  void *h_dones_out, void *h_agents_out);
+
+/* Packed host I/O (not in the reference; opt-in — the reference-layout arrays above stay the default).
+ * Three quarters of the bytes of the host loop above are bool-per-byte masks (92 payload bytes in a
+ * 128-byte record) and 59 of the 64 bytes of an ActionData record are padding.  The packed forms carry
+ * the same information:
+ *   packed mask   COG_PACKED_MASK_SIZE = 16 bytes: u32 play (bit k = play[k]), u32 remove,
+ *                 u32 move (bits 0-6) | get_from_shop << 7 (bits 7-25), u32 play_special
+ *                 — the mask words of the compact record, in the same order
+ *   packed action COG_PACKED_ACTION_SIZE = 8 bytes: u8 play, play_special, remove, move, get_from_shop, 3 x 0
+ *                 — the first eight bytes of an ActionData record
+ * so one sample + step moves 16 + 8 + 8 + 16 + 18 = 66 bytes per env over PCIe instead of 246-402.
+ * Both calls stage through device memory by DMA and return when the host arrays are complete; any
+ * *_out pointer of the step call may be NULL.  cog_vec_packed_masks writes the current packed
+ * selected (COG_MASKS_SELECTED) or merged (COG_MASKS_MERGED) masks to device (dst_is_host = 0) or host
+ * memory (dst_is_host = 1, synchronous) — what a loop needs after reset(). */
+#define COG_PACKED_MASK_SIZE 16
+#define COG_PACKED_ACTION_SIZE 8
+COG_API int cog_sampler_sample_packed_host_io(cog_sampler *s, const void *h_pmasks, void *h_pactions_out);
+COG_API int cog_vec_step_packed_host_io(cog_vec *h, const void *h_pactions, void *h_pmasks_out,
+                                        void *h_rewards_out, void *h_dones_out, void *h_agents_out);
+COG_API int cog_vec_packed_masks(cog_vec *h, void *dst, int dst_is_host, int mask_mode);
+
+/* Which implementation the *_host_io entry points use for PINNED arrays on these handles (either
+ * may be NULL): 1 zero copy, 0 staged pipeline, -1 still measuring (fewer than nine calls so far).
+ * Pageable arrays always take the staged pipeline. */
+COG_API int cog_io_path(cog_vec *h, cog_sampler *s, int *vec_path, int *sampler_path);
 
 /* ThreadedRunner<N> replacement (include/runner.h:21-134): k_steps x
  * { sample(selected_action_masks); step(actions) } in ONE persistent kernel with

@@ -358,6 +358,7 @@ struct orc_vec {
   uint8_t *obs, *masks, *dones, *infos, *agents, *actions;
   float *rewards;
   boardgen *bg;
+  int no_autoreset; /* single-env semantics: cog_env::step does not reset (src/environment.cpp:187-207) */
 };
 
 static float *e_res(orc_env *e) { return (float *)(e->obs + OBS_RES); }
@@ -865,6 +866,8 @@ int orc_reset_again(orc_vec *v) { /* vec_cog_env::reset() :33-37 */
   return 0;
 }
 
+void orc_set_autoreset(orc_vec *v, int on) { v->no_autoreset = !on; }
+
 int orc_step(orc_vec *v, const void *actions) {
   /* vec_cog_env::step / step_single include/vec_environment.h:46-61 */
   const uint8_t *a = (const uint8_t *)actions;
@@ -872,7 +875,7 @@ int orc_step(orc_vec *v, const void *actions) {
     orc_env *e = &v->env[i];
     env_step(e, a + i * ORC_ACTION_SIZE);
     v->dones[i] = e->done;
-    if (e->done) {
+    if (e->done && !v->no_autoreset) {
       int rc = env_reset(e, v->bg); /* auto-reset, no reseed */
       if (rc) return rc;
     }

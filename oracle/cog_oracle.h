@@ -39,6 +39,8 @@ int orc_reset(orc_vec *v, uint32_t seed, uint8_t n_players, uint8_t n_pieces,
               int difficulty, uint32_t max_steps);
 int orc_reset_again(orc_vec *v); /* vec_cog_env::reset() without parameters */
 int orc_step(orc_vec *v, const void *actions);
+/* on = 0: single-env semantics (no auto-reset, steps on a finished env are ignored) */
+void orc_set_autoreset(orc_vec *v, int on);
 void orc_sample(orc_vec *v, const void *masks);
 void *orc_buffer(orc_vec *v, int which);
 /* K x (sample(selected masks); step(actions)); returns seconds */

@@ -38,6 +38,7 @@ def lib():
         L.orc_reset_again.argtypes = [ctypes.c_void_p]
         L.orc_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.orc_sample.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.orc_set_autoreset.argtypes = [ctypes.c_void_p, ctypes.c_int]
         L.orc_buffer.restype = ctypes.c_void_p
         L.orc_buffer.argtypes = [ctypes.c_void_p, ctypes.c_int]
         L.orc_time_run.restype = ctypes.c_double
@@ -117,6 +118,9 @@ class OracleVec:
         m = self.selected_action_masks if masks is None else masks
         assert m.dtype == layout.action_mask_dtype and m.flags.c_contiguous
         lib().orc_sample(self._h, m.ctypes.data)
+
+    def set_autoreset(self, on):
+        lib().orc_set_autoreset(self._h, 1 if on else 0)
 
     def merged_masks(self):
         from oracle.refshim import RefVec

@@ -66,6 +66,8 @@ struct IVec {
   virtual void make_runner(size_t n_threads) = 0;
   virtual void drop_runner() = 0;
   virtual double time_run(size_t steps, int mode) = 0;
+  virtual double time_sample(size_t iters) = 0;
+  virtual double time_reset(size_t iters) = 0;
   virtual void hidden(size_t i, uint32_t *out) = 0;
 };
 
@@ -148,6 +150,22 @@ template <size_t N> struct VecImpl final : IVec {
       }
       runner->sync();
     }
+    auto t1 = std::chrono::steady_clock::now();
+    return std::chrono::duration<double>(t1 - t0).count();
+  }
+
+  // benchmarks/benchmarks.py:53-57 (time_sample): the sampler alone on the current masks
+  double time_sample(size_t iters) override {
+    const auto &masks = envs->get_selected_action_masks();
+    auto t0 = std::chrono::steady_clock::now();
+    for (size_t s = 0; s < iters; ++s) samplers->sample(masks);
+    auto t1 = std::chrono::steady_clock::now();
+    return std::chrono::duration<double>(t1 - t0).count();
+  }
+  // benchmarks/benchmarks.py:59-63 (time_reset): vec.reset() of the whole batch, sequential
+  double time_reset(size_t iters) override {
+    auto t0 = std::chrono::steady_clock::now();
+    for (size_t s = 0; s < iters; ++s) envs->reset();
     auto t1 = std::chrono::steady_clock::now();
     return std::chrono::duration<double>(t1 - t0).count();
   }
@@ -278,6 +296,24 @@ SHIM_API double ref_time_run(void *h, uint64_t steps, int mode) {
   }
 }
 
+SHIM_API double ref_time_sample(void *h, uint64_t iters) {
+  try {
+    return static_cast<IVec *>(h)->time_sample(iters);
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return -1.0;
+  }
+}
+
+SHIM_API double ref_time_reset(void *h, uint64_t iters) {
+  try {
+    return static_cast<IVec *>(h)->time_reset(iters);
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return -1.0;
+  }
+}
+
 SHIM_API void ref_hidden(void *h, uint64_t i, uint32_t *out16) {
   static_cast<IVec *>(h)->hidden(i, out16);
 }
@@ -295,6 +331,96 @@ SHIM_API uint64_t ref_sizeof(int which) {
   case 8: return sizeof(cog_env);
   default: return 0;
   }
+}
+
+// ---- the reference's SINGLE env and sampler (src/pybind/single_env.cpp:13-32, common.cpp:25-27) ----
+// cog_env needs caller-owned records (cog_env::init); the shim owns them, zeroed like a fresh allocation.
+namespace {
+struct Single {
+  ObsData obs;
+  Info info;
+  std::array<float, MAX_N_PLAYERS> rewards;
+  ActionMask selected;
+  cog_env env;
+  Single(uint32_t seed, u_char n_players, u_char n_pieces, int difficulty, unsigned max_steps)
+      : obs{}, info{}, rewards{}, selected{},
+        env(seed, n_players, n_pieces, static_cast<Difficulty>(difficulty), max_steps, false) {
+    env.init(obs, info, rewards, selected);
+  }
+};
+} // namespace
+
+SHIM_API void *ref_single_create(uint32_t seed, uint8_t n_players, uint8_t n_pieces, int difficulty,
+                                 uint32_t max_steps) {
+  try {
+    void *mem = ::operator new(sizeof(Single), std::align_val_t(alignof(Single)));
+    std::memset(mem, 0, sizeof(Single));
+    return new (mem) Single(seed, n_players, n_pieces, difficulty, max_steps);
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return nullptr;
+  }
+}
+SHIM_API void ref_single_destroy(void *h) {
+  if (!h) return;
+  static_cast<Single *>(h)->~Single();
+  ::operator delete(h, std::align_val_t(alignof(Single)));
+}
+SHIM_API int ref_single_reset(void *h, int reseed, uint32_t seed, uint8_t n_players, uint8_t n_pieces,
+                              int difficulty, uint32_t max_steps) {
+  try {
+    Single *s = static_cast<Single *>(h);
+    if (reseed) s->env.reset(seed, n_players, n_pieces, static_cast<Difficulty>(difficulty), max_steps, false);
+    else s->env.reset();
+    return 0;
+  } catch (const generate_map_failure &e) {
+    g_err = e.what();
+    return -2;
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return -1;
+  }
+}
+SHIM_API int ref_single_step(void *h, const void *action) {
+  try {
+    ActionData a{}; /* the caller's record need not be 64-byte aligned */
+    std::memcpy(&a, action, 5);
+    static_cast<Single *>(h)->env.step(a);
+    return 0;
+  } catch (const std::exception &e) {
+    g_err = e.what();
+    return -1;
+  }
+}
+// which: 0 obs, 1 selected mask, 2 rewards, 4 info
+SHIM_API void *ref_single_buffer(void *h, int which) {
+  Single *s = static_cast<Single *>(h);
+  switch (which) {
+  case 0: return &s->obs;
+  case 1: return &s->selected;
+  case 2: return s->rewards.data();
+  case 4: return &s->info;
+  default: return nullptr;
+  }
+}
+// what: 0 agent_selection, 1 done, 2 seed, 3 n_players
+SHIM_API uint32_t ref_single_get(void *h, int what) {
+  Single *s = static_cast<Single *>(h);
+  switch (what) {
+  case 0: return s->env.get_agent_selection();
+  case 1: return s->env.get_done();
+  case 2: return s->env.get_seed();
+  case 3: return s->env.get_n_players();
+  default: return 0;
+  }
+}
+SHIM_API void *ref_single_sampler_create(uint32_t seed) { return new action_sampler(seed); }
+SHIM_API void ref_single_sampler_destroy(void *h) { delete static_cast<action_sampler *>(h); }
+SHIM_API void ref_single_sampler_sample(void *h, const void *mask, void *action_out) {
+  ActionMask m{};
+  std::memcpy(&m, mask, 92); /* payload bytes; the caller's record need not be 64-byte aligned */
+  const ActionData a = static_cast<action_sampler *>(h)->sample(m);
+  std::memcpy(action_out, &a, 5);
 }
 
 // ---- standalone Map::generate driver -------------------------------------

@@ -42,6 +42,10 @@ def lib():
         L.ref_runner_destroy.argtypes = [ctypes.c_void_p]
         L.ref_time_run.restype = ctypes.c_double
         L.ref_time_run.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int]
+        L.ref_time_sample.restype = ctypes.c_double
+        L.ref_time_sample.argtypes = [ctypes.c_void_p, ctypes.c_uint64]
+        L.ref_time_reset.restype = ctypes.c_double
+        L.ref_time_reset.argtypes = [ctypes.c_void_p, ctypes.c_uint64]
         L.ref_hidden.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p]
         L.ref_sizeof.restype = ctypes.c_uint64
         L.ref_sizeof.argtypes = [ctypes.c_int]
@@ -145,6 +149,88 @@ class RefVec:
         if t < 0:
             raise RuntimeError(lib().ref_last_error().decode())
         return t
+
+
+    def time_sample(self, iters):
+        """the sampler alone, `iters` calls on the current selected masks (benchmarks.py time_sample)"""
+        t = lib().ref_time_sample(self._h, iters)
+        if t < 0:
+            raise RuntimeError(lib().ref_last_error().decode())
+        return t
+
+    def time_reset(self, iters):
+        """`iters` sequential vec.reset() calls (benchmarks.py time_reset)"""
+        t = lib().ref_time_reset(self._h, iters)
+        if t < 0:
+            raise RuntimeError(lib().ref_last_error().decode())
+        return t
+
+
+class RefSingle:
+    """The reference's single cog_env (src/pybind/single_env.cpp:13-32) with shim-owned records."""
+
+    def __init__(self, seed, n_players=4, n_pieces=3, difficulty=0, max_steps=100000):
+        L = lib()
+        L.ref_single_create.restype = ctypes.c_void_p
+        L.ref_single_create.argtypes = [ctypes.c_uint32, ctypes.c_uint8, ctypes.c_uint8, ctypes.c_int, ctypes.c_uint32]
+        L.ref_single_destroy.argtypes = [ctypes.c_void_p]
+        L.ref_single_reset.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_uint32, ctypes.c_uint8, ctypes.c_uint8,
+                                       ctypes.c_int, ctypes.c_uint32]
+        L.ref_single_step.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.ref_single_buffer.restype = ctypes.c_void_p
+        L.ref_single_buffer.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        L.ref_single_get.restype = ctypes.c_uint32
+        L.ref_single_get.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        self._h = L.ref_single_create(seed & 0xFFFFFFFF, n_players, n_pieces, int(difficulty), max_steps)
+        b = lambda w: L.ref_single_buffer(self._h, w)
+        self.observations = _view(b(0), layout.obs_dtype, (1,))
+        self.selected_action_masks = _view(b(1), layout.action_mask_dtype, (1,))
+        self.rewards = _view(b(2), np.dtype(np.float32), (1, 4))
+        self.infos = _view(b(4), layout.info_dtype, (1,))
+
+    def close(self):
+        if self._h:
+            lib().ref_single_destroy(self._h)
+            self._h = None
+
+    def reset(self, seed=None, n_players=4, n_pieces=3, difficulty=0, max_steps=100000):
+        rc = lib().ref_single_reset(self._h, 0 if seed is None else 1, (seed or 0) & 0xFFFFFFFF, n_players, n_pieces,
+                                    int(difficulty), max_steps)
+        if rc:
+            raise RuntimeError(lib().ref_last_error().decode())
+
+    def step(self, action):
+        assert action.dtype == layout.action_dtype
+        if lib().ref_single_step(self._h, action.ctypes.data):
+            raise RuntimeError(lib().ref_last_error().decode())
+
+    agent_selection = property(lambda self: lib().ref_single_get(self._h, 0))
+    done = property(lambda self: bool(lib().ref_single_get(self._h, 1)))
+    seed = property(lambda self: lib().ref_single_get(self._h, 2))
+    n_players = property(lambda self: lib().ref_single_get(self._h, 3))
+
+
+class RefSampler:
+    """The reference's single action_sampler (include/sampler.h, bound at src/pybind/common.cpp:25-27)."""
+
+    def __init__(self, seed):
+        L = lib()
+        L.ref_single_sampler_create.restype = ctypes.c_void_p
+        L.ref_single_sampler_create.argtypes = [ctypes.c_uint32]
+        L.ref_single_sampler_destroy.argtypes = [ctypes.c_void_p]
+        L.ref_single_sampler_sample.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        self._h = L.ref_single_sampler_create(seed & 0xFFFFFFFF)
+
+    def sample(self, mask):
+        assert mask.dtype == layout.action_mask_dtype
+        out = np.zeros(1, dtype=layout.action_dtype)
+        lib().ref_single_sampler_sample(self._h, mask.ctypes.data, out.ctypes.data)
+        return out
+
+    def close(self):
+        if self._h:
+            lib().ref_single_sampler_destroy(self._h)
+            self._h = None
 
 
 def map_generate(seed, n_pieces, difficulty, rows=48, max_hexes=2048):

@@ -433,3 +433,50 @@ def two_player_clean_seeds(seed, n, difficulty, max_steps, steps, want=12):
     finally:
         o.close()
     return [seed + i for i in clean[:want]]
+
+
+def run_packed_io_parity(library, oracle_cls, n, seed, difficulty, max_steps, steps, regime="A", pinned=False):
+    """The packed host-I/O entry points (16-byte masks, 8-byte actions) driven like a host policy loop,
+    against the oracle at every step; also cog_vec_packed_masks (selected and merged) against the
+    packed form of the oracle's records."""
+    o = oracle_cls(n, seed)
+    c = Candidate(library, n, seed)
+    try:
+        o.reset(seed, 4, 3, difficulty, max_steps)
+        c.reset(seed, 4, 3, difficulty, max_steps)
+        pmasks = _host_array(n, layout.packed_mask_dtype, pinned)
+        pactions = _host_array(n, layout.packed_action_dtype, pinned)
+        rewards = _host_array((n, 4), np.float32, pinned)
+        dones = _host_array(n, np.bool_, pinned)
+        agents = _host_array(n, np.uint8, pinned)
+        c.vec.packed_masks(out=pmasks)
+        assert np.array_equal(pmasks, layout.pack_masks(o.selected_action_masks)), "packed masks after reset"
+        assert np.array_equal(pb(layout.unpack_masks(pmasks)), pb(o.selected_action_masks))
+        n_done = 0
+        for s in range(steps):
+            if regime == "M":
+                m = merged_masks(oracle_snapshot(o))
+                o.sample(m)
+                pm = c.vec.packed_masks(merged=True)
+                assert np.array_equal(pm, layout.pack_masks(m)), "step %d: packed merged masks" % s
+            else:
+                o.sample()
+                pm = pmasks
+            c.smp.sample_packed_host_io(pm, pactions)
+            want = pb(o.actions)
+            got = np.ascontiguousarray(pactions).view(np.uint8).reshape(n, 8)
+            assert np.array_equal(got[:, :5], want) and not got[:, 5:].any(), "step %d: actions" % s
+            assert np.array_equal(pb(c.smp.read_actions()), want), "step %d: sampler's own ActionData buffer" % s
+            o.step()
+            c.vec.step_packed_host_io(pactions, pmasks, rewards, dones, agents)
+            assert np.array_equal(pmasks, layout.pack_masks(o.selected_action_masks)), "step %d: masks" % s
+            assert np.array_equal(rewards, o.rewards) and np.array_equal(dones, o.dones), "step %d" % s
+            assert np.array_equal(agents, o.agent_selection), "step %d: agent_selection" % s
+            n_done += int(dones.sum())
+        bad = first_mismatch(c.snapshot(), oracle_snapshot(o))
+        assert bad is None, bad
+        assert c.vec.stats()["env_steps"] == n * steps
+        return n_done
+    finally:
+        c.close()
+        o.close()

@@ -171,3 +171,9 @@ def test_emulated_two_players_vs_reference(emu):
             bad = parity.first_mismatch(c.snapshot(), parity.oracle_snapshot(r))
             assert bad is None, "seed %d step %d: %s" % (seed, s, bad)
         c.close(); r.close()
+
+
+@pytest.mark.parametrize("regime", ["A", "M"])
+def test_emulated_packed_host_io(emu, oracle_cls, regime):
+    """16-byte masks / 8-byte actions through cog_*_packed_host_io == the oracle at every step"""
+    assert parity.run_packed_io_parity(emu, oracle_cls, 12, 99, layout.HARD, 10, 200, regime) > 0

@@ -178,3 +178,11 @@ def test_rollout_ring_and_compact_obs(cuda_lib, oracle_cls, n, merged, difficult
     assert dones > 0
     if max_steps > 100:
         assert wins > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,regime,pinned", [(16384, "A", True), (4096, "M", False), (1024, "M", True)])
+def test_packed_host_io(cuda_lib, oracle_cls, n, regime, pinned):
+    """The packed host-I/O entry points (16-byte masks, 8-byte actions: 66 bytes per env-step over PCIe)
+    == the oracle at every step, pageable and pinned arrays."""
+    assert parity.run_packed_io_parity(cuda_lib, oracle_cls, n, 99, layout.HARD, 10, 120, regime, pinned=pinned) > 0
