@@ -8,41 +8,26 @@ line (see the contract in the task description / DESIGN.md §Measurement).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+The line's parts (bench_parts.py holds the side measurements):
+  value / roofline     the fused kernel, device resident (regime A = the reference's own benchmark flow)
+  extra                regime M (every branch of step live), reset-heavy configs[3], resets/s, the
+                       per-step device API loop (two kernels and one), rollout ring — each with its own
+                       fraction of the SURVEY 8(d) roofline
+  config4              (N > 1) BASELINE configs[4]: 1 M envs split over the ranks, HARD, strong scaling
+  e2e                  host policy loop through the C ABI with host arrays, copies inside the timed region
+  cpu_baseline, cpu_legs   the unmodified reference on this box's host cores
 """
 import argparse
 import json
 import os
-import subprocess
 import sys
-import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# SURVEY §8(d): payload bytes that must move per sample+step when every exported buffer is
-# kept current each step (391 read + 305 written)
-ALGO_BYTES_PER_ENV_STEP = 696
-ALGO_BYTES_PER_RESET = 19440  # SURVEY §8(d)
-FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md
-
-# BASELINE.json configs (0-based index); [2] is the headline single-GPU workload
-WORKLOADS = {
-    2: {"workload": "BASELINE configs[2]: 65,536 envs per GPU, 4 players, 3 pieces, MEDIUM, "
-                    "max_steps 100000, masked random sampler, persistent fused step+sample kernel",
-        "n_envs_per_gpu": 65536, "n_players": 4, "n_pieces": 3, "difficulty": "MEDIUM",
-        "max_steps": 100000, "seed": 12345},
-    3: {"workload": "BASELINE configs[3] (reset-heavy): 65,536 envs per GPU, 2 players, 3 pieces, HARD, "
-                    "max_steps 8 turns, fused kernel with procedural board generation on every episode end",
-        "n_envs_per_gpu": 65536, "n_players": 2, "n_pieces": 3, "difficulty": "HARD",
-        "max_steps": 8, "seed": 12345},
-    4: {"workload": "BASELINE configs[4]: 1,048,576 envs sharded over the GPUs, 4 players, 3 pieces, HARD, "
-                    "max_steps 100000, fused kernel, NCCL-reduced episode statistics",
-        "n_envs_per_gpu": None, "n_envs_total": 1 << 20, "n_players": 4, "n_pieces": 3, "difficulty": "HARD",
-        "max_steps": 100000, "seed": 12345},
-}
-WORKLOAD = dict(WORKLOADS[2])
-DIFFICULTY = {"EASY": 0, "MEDIUM": 1, "HARD": 2}
+import bench_parts as bp  # noqa: E402
 
 
 def parse():
@@ -52,136 +37,22 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--inner", type=int, default=1024, help="fused sample+step iterations per launch")
-    ap.add_argument("--config", type=int, default=2, choices=sorted(WORKLOADS), help="BASELINE.json configs index")
+    ap.add_argument("--config", type=int, default=2, choices=sorted(bp.WORKLOADS), help="BASELINE.json configs index")
     ap.add_argument("--envs", type=int, default=None, help="envs per GPU (default: the config's)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cpu-legs", action="store_true", help="skip the thread sweep / reset / sample CPU legs")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-resets", action="store_true")
-    ap.add_argument("--no-side", action="store_true", help="skip the regime-M / reset-heavy side measurements")
+    ap.add_argument("--no-side", action="store_true", help="skip the regime-M / reset-heavy / API-loop side measurements")
+    ap.add_argument("--no-config4", action="store_true", help="skip the configs[4] leg of a multi-GPU run")
     args = ap.parse_args()
-    WORKLOAD.clear()
-    WORKLOAD.update(WORKLOADS[args.config])
+    args.workload = dict(bp.WORKLOADS[args.config])
     if args.envs is None:
-        args.envs = WORKLOAD["n_envs_per_gpu"] or WORKLOAD["n_envs_total"] // max(1, args.gpus)
-    WORKLOAD["n_envs_per_gpu"] = args.envs
+        args.envs = args.workload["n_envs_per_gpu"] or args.workload["n_envs_total"] // max(1, args.gpus)
+    args.workload["n_envs_per_gpu"] = args.envs
     return args
 
 
-def peak_hbm():
-    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(p):
-        try:
-            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
-        except Exception:
-            pass
-    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
-
-
-class ClockSampler(threading.Thread):
-    """nvidia-smi clocks/throttle reasons DURING the timed region (profiling recipe)."""
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
-
-    def __init__(self, index):
-        super().__init__(daemon=True)
-        self.index, self.rows, self._halt = index, [], threading.Event()
-
-    def run(self):
-        while not self._halt.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([x.strip() for x in out.strip().split(",")])
-            except Exception:
-                pass
-            self._halt.wait(0.1)
-
-    def finish(self):
-        self._halt.set()
-        self.join(timeout=6)
-        sm, mx, reasons = [], 0.0, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            if len(r) < 6:
-                continue
-            try:
-                sm.append(float(r[0])); mx = max(mx, float(r[1]))
-            except ValueError:
-                continue
-            for name, v in zip(names, r[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm)}
-
-
-# --------------------------------------------------------------------------- reference arm
-def run_reference(args, bounded_seconds=None):
-    """The reference's own CPU implementation of the path (oracle/_ref = its unmodified
-    sources + ThreadedRunner), all usable host threads, same config/metric/unit.
-    Each step is a bounded sample of the workload: `ref_inner` sample+step iterations."""
-    from oracle import refshim
-    kind = "reference"
-    if not refshim.available():
-        kind = "port"
-    n = args.envs
-    if refshim.available():  # the reference's templates are instantiated for these sizes only
-        n = max(k for k in refshim.SUPPORTED_N if k <= n)
-    cores = os.cpu_count() or 1
-    try:
-        cores = len(os.sched_getaffinity(0))
-    except Exception:
-        pass
-    diff = DIFFICULTY[WORKLOAD["difficulty"]]
-    npl = WORKLOAD["n_players"]
-    if kind == "reference" and npl < 4:
-        npl = 4  # fewer than 4 players is undefined behaviour in the reference (SURVEY App. A#13)
-    if kind == "reference":
-        threads = max(1, min(cores - 1, 32))  # workers busy-wait and pin; never oversubscribe
-        v = refshim.RefVec(n, WORKLOAD["seed"])
-        v.reset(WORKLOAD["seed"], npl, 3, diff, WORKLOAD["max_steps"])
-        v.runner(threads)
-        mode = 1  # ThreadedRunner async (the reference's fastest mode)
-        run = lambda k: v.time_run(k, mode)
-        used = threads
-        how = "unmodified reference ThreadedRunner<%d> async, %d pinned worker threads" % (n, threads)
-    else:
-        from oracle import port
-        v = port.OracleVec(n, WORKLOAD["seed"])
-        v.reset(WORKLOAD["seed"], npl, 3, diff, WORKLOAD["max_steps"])
-        run = v.time_run
-        used = 1
-        how = "oracle port (scalar C), 1 thread"
-    # calibrate the bounded sample: ~1 s per step
-    t = run(2)
-    ref_inner = max(1, int(2 * 1.0 / max(t, 1e-6)))
-    if bounded_seconds is not None:  # cpu_baseline leg of the b200 arm: one bounded run
-        ref_inner = max(1, int(2 * bounded_seconds / max(t, 1e-6)))
-        dt = run(ref_inner)
-        return {"value": n * ref_inner / dt, "unit": "env-steps/s", "cores": used, "kind": kind,
-                "sample": "%s; %d sample+step iterations on %d envs (%.1f s)" % (how, ref_inner, n, dt)}
-    for _ in range(args.warmup):
-        run(ref_inner)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        run(ref_inner)
-    dt = time.perf_counter() - t0
-    value = n * ref_inner * args.steps / dt
-    cfg = dict(WORKLOAD)
-    cfg["n_envs_per_gpu"] = n
-    cfg["note"] = "each step = %d sample+step iterations on all envs (bounded sample)" % ref_inner
-    line = {"impl": "reference", "metric": "env-steps/sec (random masked policy)", "value": value,
-            "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "u8/u32 integer (f32 exports)", "data": "synthetic",
-            "config": cfg,
-            "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": used, "kind": kind, "sample": how},
-            "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
-
-
-# --------------------------------------------------------------------------- b200 arm
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -190,289 +61,97 @@ def main():
 
     if args.impl == "reference":
         if rank == 0:
-            run_reference(args)
+            print(json.dumps(bp.reference_arm(args, world)))
         return
 
-    import numpy as np
     import torch
     import torch.distributed as dist
-    from gym_eldorado_b200 import capi, layout, shard
+    from gym_eldorado_b200 import capi, shard
 
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ctx = bp.Ctx(args, rank, local_rank, world)
+    W = args.workload
     L = capi.lib()
     n = args.envs
     offset = rank * n  # weak scaling: every GPU owns its own slice of global env indices
-    if WORKLOAD.get("n_envs_total") and args.envs * world == WORKLOAD["n_envs_total"]:
-        offset, stop = shard.shard_range(rank, world, WORKLOAD["n_envs_total"])  # config 4: fixed total
+    if W.get("n_envs_total") and args.envs * world == W["n_envs_total"]:
+        offset, stop = shard.shard_range(rank, world, W["n_envs_total"])  # configs[4]: fixed total
         n = stop - offset
     vec = capi.VecHandle(n, offset, local_rank, None, L)
-    smp = capi.SamplerHandle(n, WORKLOAD["seed"], offset, local_rank, None, L)
-    vec.reset(WORKLOAD["seed"], WORKLOAD["n_players"], 3, DIFFICULTY[WORKLOAD["difficulty"]], WORKLOAD["max_steps"])
+    smp = capi.SamplerHandle(n, W["seed"], offset, local_rank, None, L)
+    vec.reset(W["seed"], W["n_players"], W["n_pieces"], bp.DIFFICULTY[W["difficulty"]], W["max_steps"])
     launches0 = L.cog_kernel_launches()
-    stats_t = torch.zeros(len(capi.STAT_NAMES), dtype=torch.int64, device="cuda")
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def one_step():
-        vec.run_fused(smp, args.inner)
-
+    # ---- the timed region: K launches of the fused kernel --------------------------------------
     for _ in range(args.warmup):
-        one_step()
-    barrier()
-    clocks = ClockSampler(local_rank)
+        vec.run_fused(smp, args.inner)
+    ctx.barrier()
+    clocks = bp.ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
     vec.stats_reset()
     launches_timed0 = L.cog_kernel_launches()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    kernel_ms = []
     ev0.record()
     for _ in range(args.steps):
-        one_step()
-        kernel_ms.append(None)
+        vec.run_fused(smp, args.inner)
     # the one data-path-free collective: aggregate episode statistics over NVLink
-    tot = shard.reduce_stats(vec.stats(), device="cuda")
-    stats_t.copy_(torch.tensor([tot[k] for k in capi.STAT_NAMES], dtype=torch.int64))
+    stats = shard.reduce_stats(vec.stats(), device="cuda")
     ev1.record()
-    barrier()
-    ms = ev0.elapsed_time(ev1)
+    ctx.barrier()
+    ms = ctx.max_over_ranks(ev0.elapsed_time(ev1))
     clk = clocks.finish() if rank == 0 else None
     launches_timed = L.cog_kernel_launches() - launches_timed0
-    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    total_env_steps = int(stats_t[0].item())
-    assert total_env_steps == world * n * args.inner * args.steps, "work was skipped"
-    value = total_env_steps / (ms * 1e-3)
+    assert stats["env_steps"] == world * n * args.inner * args.steps, "work was skipped"
+    value = stats["env_steps"] / (ms * 1e-3)
 
-    # per-launch duration of the dominant kernel, CUDA events on the launching stream
+    # per-launch duration of the dominant kernel, CUDA events recorded by the library on its own stream
     per_launch = []
     for _ in range(max(3, min(args.steps, 10))):
-        one_step()
+        vec.run_fused(smp, args.inner)
         per_launch.append(vec.last_kernel_ms())
     k_ms = sum(per_launch) / len(per_launch)
-    peak, peak_src = peak_hbm()
-    algo_bytes = ALGO_BYTES_PER_ENV_STEP * n * args.inner
-    achieved = algo_bytes / (k_ms * 1e-3) / 1e9
-    traffic = None
-    tp = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tp):
-        try:
-            tj = json.load(open(tp))
-            if tj.get("inner") == args.inner and tj.get("envs") == n:
-                traffic = tj.get("dram_bytes_per_launch")
-        except Exception:
-            pass
-    roofline = {"bound": "hbm", "kernel": "cog::k_step_fused (+ k_step_tail for finished episodes)", "achieved": achieved,
-                "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": k_ms,
-                "note": "696 B per env-step (SURVEY 8d) x envs x inner; the fused kernel keeps env state in "
-                        "registers, so real DRAM traffic is far lower and the kernel is issue-bound"}
+    sm_mhz = (clk or {}).get("sm_mhz") or 1965.0
+    roofline = bp.roofline_fused(n, args.inner, k_ms, sm_mhz, stats)
 
-    # procedural board generation: full-batch resets (the reference's `time_reset` analogue)
-    resets = None
+    extra = {}
     if not args.no_resets:
-        for _ in range(2):
-            vec.reset()
-        r_iters = 10
-        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        barrier()
-        r0.record()
-        for _ in range(r_iters):
-            vec.reset()
-        r1.record()
-        barrier()
-        r_ms = r0.elapsed_time(r1) / r_iters
-        tr = torch.tensor([r_ms], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(tr, op=dist.ReduceOp.MAX)
-        r_ms = float(tr.item())
-        resets = {"value": world * n / (r_ms * 1e-3), "unit": "resets/s", "ms_per_batch_reset": r_ms,
-                  "kernel": "cog::k_reset", "algorithmic_bytes_per_reset": ALGO_BYTES_PER_RESET,
-                  "achieved_GBs_per_gpu": ALGO_BYTES_PER_RESET * n / (r_ms * 1e-3) / 1e9,
-                  "frac_of_hbm_peak": ALGO_BYTES_PER_RESET * n / (r_ms * 1e-3) / 1e9 / peak,
-                  "note": "vec.reset() of all %d envs per GPU, %d timed launches (board generation is "
-                          "latency/issue bound, not HBM bound)" % (n, r_iters)}
-        # back to the benchmark trajectory state is not needed: e2e below starts from whatever state this leaves
-
-    # the other single-GPU workloads SURVEY §8(d) asks for, as side measurements (same kernels,
-    # clearly labelled; the headline stays the config above): regime M = actions sampled from the
-    # merged legal mask (moves, purchases, wins: every branch of step live), and the reset-heavy
-    # configs[3] (HARD, 8 turns per episode, 2 players: board generation inside the step loop)
-    side = None
+        extra["resets"] = bp.measure_resets(ctx, vec, n)
     if not args.no_side:
-        side = {}
-        # ... and the rollout writer: the same fused loops appending one 256-byte compact
-        # record per env-step to a device ring of `slots` time slots
-        for name, diffc, npl, max_steps, merged, slots in (
-                ("regime_M_merged_masks", WORKLOAD["difficulty"], 4, 100000, True, 0),
-                ("reset_heavy_configs3", "HARD", 2, 8, False, 0),
-                ("rollout_ring", WORKLOAD["difficulty"], 4, 100000, False, 256),
-                ("rollout_ring_regime_M", WORKLOAD["difficulty"], 4, 100000, True, 256)):
-            v2 = capi.VecHandle(n, offset, local_rank, None, L)
-            s2 = capi.SamplerHandle(n, WORKLOAD["seed"], offset, local_rank, None, L)
-            v2.reset(WORKLOAD["seed"], npl, 3, DIFFICULTY[diffc], max_steps)
-            if slots:
-                v2.rollout_attach(slots)
-            inner2, reps = 256, 5
-            for _ in range(2):
-                v2.run_fused(s2, inner2, merged=merged)
-            v2.stats_reset()
-            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            barrier()
-            a0.record()
-            for _ in range(reps):
-                v2.run_fused(s2, inner2, merged=merged)
-            a1.record()
-            barrier()
-            tm = torch.tensor([a0.elapsed_time(a1)], dtype=torch.float64, device="cuda")
-            if world > 1:
-                dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-            st2 = shard.reduce_stats(v2.stats(), device="cuda")
-            sec = float(tm.item()) * 1e-3
-            side[name] = {"value": st2["env_steps"] / sec, "unit": "env-steps/s", "resets_per_s": st2["resets"] / sec,
-                          "episodes": st2["episodes"], "wins": sum(st2["wins_seat%d" % k] for k in range(4)),
-                          "truncations": st2["truncations"], "travelled_hexes": st2["travelled_hexes"],
-                          "cards_added": st2["cards_added"],
-                          "config": "%d envs per GPU, %d players, %s, max_steps %d, %d launches x %d iterations, %s" % (
-                              n, npl, diffc, max_steps, reps, inner2,
-                              "merged legal masks" if merged else "selected_action_masks")}
-            if slots:
-                side[name]["ring"] = "%d slots x %d envs x %d B per GPU" % (slots, n, layout.compact_dtype.itemsize)
-                side[name]["ring_write_GBs_per_gpu"] = (st2["env_steps"] / world) * layout.compact_dtype.itemsize / sec / 1e9
-            v2.close(); s2.close()
-
-    # the reference's own Python loop on DEVICE buffers (zero copy): sample(selected masks); step(actions),
-    # two single-step kernel launches per iteration, nothing crosses PCIe
-    api_loop = None
-    if not args.no_side:
-        masks_ptr = vec.buffer(layout.BUF_SELECTED_MASKS)[0]
-        act_ptr = smp.actions_ptr()
-        it = 200
-        for _ in range(10):
-            smp.sample_device(masks_ptr); vec.step_device(act_ptr)
-        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        barrier()
-        a0.record()
-        for _ in range(it):
-            smp.sample_device(masks_ptr); vec.step_device(act_ptr)
-        a1.record()
-        barrier()
-        tm = torch.tensor([a0.elapsed_time(a1)], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-        api_loop = {"value": world * n * it / (float(tm.item()) * 1e-3), "unit": "env-steps/s",
-                    "us_per_iteration": float(tm.item()) * 1e3 / it,
-                    "api": "sampler.sample(envs.selected_action_masks); envs.step(sampler.get_actions()) on device "
-                           "buffers, k_sample + k_step_single per iteration, %d iterations" % it}
-
-    # end to end through the reference-facing call shape with HOST buffers: every step
-    # copies that step's inputs (masks for sample(), actions for step()) from pinned host
-    # memory and reads the step's results back
-    e2e = None
-    if not args.no_e2e:
-        mdt, adt = layout.action_mask_dtype, layout.action_dtype
-        h_masks = torch.empty(n * mdt.itemsize, dtype=torch.uint8).pin_memory()
-        h_actions = torch.empty(n * adt.itemsize, dtype=torch.uint8).pin_memory()
-        h_rew = torch.empty(n * 16, dtype=torch.uint8).pin_memory()
-        h_done = torch.empty(n, dtype=torch.uint8).pin_memory()
-        h_agent = torch.empty(n, dtype=torch.uint8).pin_memory()
-        np_masks = h_masks.numpy().view(mdt)
-        np_actions = h_actions.numpy().view(adt)
-        vec.read(layout.BUF_SELECTED_MASKS, np_masks)
-
-        np_rew = h_rew.numpy().view(np.float32).reshape(n, 4)
-        np_done = h_done.numpy().view(np.bool_)
-        np_agent = h_agent.numpy()
-
-        def e2e_step_serial():  # one blocking call per copy / kernel (the round-1 path)
-            smp.sample_host(np_masks)                 # H2D masks, sample
-            smp.read_actions(np_actions)              # D2H actions (sync)
-            vec.step_host(np_actions)                 # H2D actions, step
-            vec.read(layout.BUF_SELECTED_MASKS, np_masks)   # D2H next masks
-            L.cog_vec_read(vec._h, layout.BUF_REWARDS, h_rew.data_ptr(), h_rew.numel())
-            L.cog_vec_read(vec._h, layout.BUF_DONES, h_done.data_ptr(), h_done.numel())
-            L.cog_vec_read(vec._h, layout.BUF_AGENT_SELECTION, h_agent.data_ptr(), h_agent.numel())
-
-        def e2e_step():  # same data flow, two calls.  Pinned arrays: the kernels read the inputs from and
-            # write masks / actions to the host arrays themselves (zero copy); COG_IO_ZEROCOPY=0 or pageable
-            # arrays: staging copies and kernels pipelined chunk by chunk on two streams
-            smp.sample_host_io(np_masks, np_actions)  # host masks -> sample -> host actions
-            vec.step_host_io(np_actions, np_masks, np_rew, np_done, np_agent)  # host actions -> step -> host results
-
-        def timed(fn, iters):
-            for _ in range(12):  # also covers the library's nine-call measurement of its two host-I/O paths
-                fn()
-            barrier()
-            t0 = time.perf_counter()
-            for _ in range(iters):
-                fn()
-            barrier()
-            tt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-            if world > 1:
-                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            return world * n * iters / float(tt.item())
-
-        e2e_iters = max(20, args.steps * 5)
-        serial = timed(e2e_step_serial, e2e_iters)
-        vec.read(layout.BUF_SELECTED_MASKS, np_masks)
-        os.environ["COG_IO_ZEROCOPY"] = "0"
-        piped = timed(e2e_step, e2e_iters)
-        os.environ["COG_IO_ZEROCOPY"] = "1"
-        vec.read(layout.BUF_SELECTED_MASKS, np_masks)
-        zero = timed(e2e_step, e2e_iters)
-        os.environ.pop("COG_IO_ZEROCOPY")
-        vec.read(layout.BUF_SELECTED_MASKS, np_masks)
-        direct = timed(e2e_step, e2e_iters)   # the default: the library measures both paths and keeps the faster
-        # bytes that cross the link per step on the zero-copy path: the kernels pull 3 of the 4 sectors of every
-        # ActionMask (92 payload bytes) and 1 of the 2 of every ActionData, and push 92 B of mask + 8 B of action;
-        # rewards / dones / agent_selection go by DMA.  (The DMA paths move the whole records: 192 B each way.)
-        h2d = n * (96 + 32)
-        d2h = n * (92 + 8 + 16 + 1 + 1)
-        full = n * (mdt.itemsize + adt.itemsize)
-        e2e = {"value": direct, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-               "api": "host policy loop, every step: cog_sampler_sample_host_io(host masks -> host actions); "
-                      "cog_vec_step_host_io(host actions -> host masks, rewards, dones, agent_selection); "
-                      "single-step kernels; pinned host arrays: either read and written by the kernels themselves "
-                      "over PCIe (zero copy, small outputs by DMA) or staged through a chunked copy/compute "
-                      "pipeline — the library times both on its first calls and keeps the faster; %d iterations"
-                      % e2e_iters,
-               "zero_copy_value": zero, "dma_pipeline_value": piped, "serial_calls_value": serial,
-               "dma_bytes_per_step": {"h2d": full, "d2h": full + n * 18},
-               "note": "value = default (auto-selected path); zero_copy_value / dma_pipeline_value = the same calls "
-                       "with COG_IO_ZEROCOPY=1 / 0 (the latter is what pageable arrays get: staging copies + kernels "
-                       "pipelined in two chunks on two streams); h2d/d2h_bytes_per_step count the zero-copy path, "
-                       "dma_bytes_per_step the staged one; serial_calls_value = one blocking call per copy / kernel"}
+        extra.update(bp.measure_side_workloads(ctx, L, n, offset, sm_mhz))
+        extra.update(bp.measure_api_loop(ctx, vec, smp, n))
+    config4 = None
+    if world > 1 and not args.no_config4 and args.config == 2:
+        config4 = bp.measure_config4(ctx, L)
+    e2e = None if args.no_e2e else bp.measure_e2e(ctx, L, vec, smp, n, args.steps)
     launches = L.cog_kernel_launches() - launches0
 
-    cpu = None
+    cpu, legs = None, None
     if rank == 0 and not args.no_cpu_baseline:
         try:
-            cpu = run_reference(args, bounded_seconds=10.0)
+            cpu = bp.cpu_baseline(args, bounded_seconds=10.0)
+            if not args.no_cpu_legs and world == 1:
+                legs = bp.cpu_legs(args)
         except Exception as e:  # the baseline is reporting, never the product path
-            cpu = {"error": repr(e)}
+            cpu = cpu or {"error": repr(e)}
+            legs = {"error": repr(e)}
 
     if rank == 0:
-        cfg = dict(WORKLOAD)
-        cfg.update({"n_envs_per_gpu": n, "inner_steps_per_launch": args.inner,
-                    "parallelism": "env-index sharding x%d, no data-path collective" % world,
-                    "l2": "working set %.2f GB per GPU (> 126 MB L2); no flush needed" %
-                          (n * (17216 + 128 + 192 + 18 + 4 * 288 + 2304) / 1e9)})
-        line = {"metric": "env-steps/sec (random masked policy)", "value": value, "unit": "env-steps/s",
+        line = {"metric": bp.METRIC, "value": value, "unit": "env-steps/s",
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-                "higher_is_better": True, "scaling": "strong" if WORKLOAD.get("n_envs_total") else "weak",
-                "vs_baseline": None,
-                "dtype": "u8/u32 integer (f32 exports)", "data": "synthetic", "config": cfg,
-                "roofline": roofline, "resets": resets, "side_workloads": side, "device_api_loop": api_loop, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_timed,
-                "gpu_launches_total": launches, "clocks": clk,
-                "episode_stats": dict(zip(capi.STAT_NAMES, (int(x) for x in stats_t.tolist())))}
+                "higher_is_better": True, "scaling": "strong" if W.get("n_envs_total") else "weak",
+                "vs_baseline": None, "dtype": bp.DTYPE, "data": "synthetic",
+                "config": bp.config_of(args, world), "roofline": roofline,
+                "regime_M": (extra.get("regime_M_merged_masks") or {}).get("summary"),
+                "extra": extra, "config4": config4, "cpu_baseline": cpu, "cpu_legs": legs, "e2e": e2e,
+                "gpu_launches": launches_timed, "gpu_launches_total": launches, "clocks": clk,
+                "episode_stats": stats,
+                "note": "headline = regime A, the reference's own README / pytest / asv flow (actions sampled from "
+                        "selected_action_masks: only play / null ever occur, %d episodes finished in the timed region); "
+                        "regime_M = the same kernels with every branch of step live" % stats["episodes"]}
         print(json.dumps(line))
     vec.close()
     smp.close()

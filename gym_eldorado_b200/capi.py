@@ -46,6 +46,12 @@ SYMBOLS = {
     "cog_sampler_sample_host_io": (_int, [_vp, _vp, _vp]),
     "cog_vec_step_host_io": (_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "cog_io_path": (_int, [_vp, _vp, _P(_int), _P(_int)]),
+    "cog_vec_wait_stream": (_int, [_vp, _vp]),
+    "cog_vec_release_to_stream": (_int, [_vp, _vp]),
+    "cog_sampler_wait_stream": (_int, [_vp, _vp]),
+    "cog_sampler_release_to_stream": (_int, [_vp, _vp]),
+    "cog_vec_stream": (_int, [_vp, _P(_vp)]),
+    "cog_sampler_stream": (_int, [_vp, _P(_vp)]),
     "cog_sampler_sample_packed_host_io": (_int, [_vp, _vp, _vp]),
     "cog_vec_step_packed_host_io": (_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "cog_vec_packed_masks": (_int, [_vp, _vp, _int, _int]),

@@ -100,6 +100,8 @@ struct cog_vec {
   cudaStream_t io[2] = {nullptr, nullptr}; /* copy/compute pipeline of the *_host_io entry points */
   cudaEvent_t io_ev[4] = {nullptr, nullptr, nullptr, nullptr};
   IoTune tune;
+  int *err_host = nullptr;     /* host address of B.err (mapped pinned memory) */
+  cudaEvent_t ev_in = nullptr, ev_order = nullptr; /* input copy done / cross-stream ordering */
   void *pk_actions = nullptr, *pk_masks = nullptr; /* device staging of the packed host-I/O entry points */
   uint64_t host_steps = 0;     /* env-steps of single-step calls since the last stats reset (n per call) */
 };
@@ -113,6 +115,7 @@ struct cog_sampler {
   uint8_t *actions = nullptr;
   void *staging = nullptr; /* device copy of host masks for cog_sampler_sample_host */
   void *pk_masks = nullptr, *pk_actions = nullptr; /* device staging of the packed host-I/O entry points */
+  cudaEvent_t ev_in = nullptr, ev_order = nullptr;
   cudaStream_t io[2] = {nullptr, nullptr};
   cudaEvent_t io_ev[4] = {nullptr, nullptr, nullptr, nullptr};
   IoTune tune;
@@ -120,12 +123,16 @@ struct cog_sampler {
 
 namespace {
 
+/* Wait for the handle's stream, then report a device-side failure (board generation during a reset or an
+ * auto-reset).  The flag lives in mapped pinned HOST memory (the kernels write it over PCIe only when
+ * something fails), so every synchronising entry point can afford the check: no copy, no extra launch. */
 int check_device_error(cog_vec *h) {
-  int err[2] = {0, 0};
-  CK(cudaMemcpyAsync(err, h->B.err, sizeof(err), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
-  if (err[0] == 0) return COG_OK;
-  CK(cudaMemsetAsync(h->B.err, 0, sizeof(err), h->stream));
+  volatile int *flag = h->err_host;
+  if (flag[0] == 0) return COG_OK;
+  const int err[2] = {flag[0], flag[1]};
+  flag[0] = 0;
+  flag[1] = 0;
   char msg[160];
   if (err[0] == COG_ERR_MAP_FAILURE)
     std::snprintf(msg, sizeof msg, "Failed to generate map in specified maximum number of attempts (env %d)", err[1]);
@@ -270,13 +277,22 @@ int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device, void 
   CK(cudaSetDevice(device));
   cog_vec *h = new (std::nothrow) cog_vec;
   if (!h) return fail(COG_ERR_INVALID, "out of host memory");
+  /* from here on every failure path releases the handle and whatever it already owns */
+#define CKH(call)                          \
+  do {                                     \
+    cudaError_t e_ = (call);               \
+    if (e_ != cudaSuccess) {               \
+      cog_vec_destroy(h);                  \
+      return cuda_fail(e_, #call);         \
+    }                                      \
+  } while (0)
   h->n = n_envs;
   h->offset = env_index_offset;
   h->device = device;
   h->stream = (cudaStream_t)stream; /* NULL = the device's default stream */
-  CK(cudaEventCreate(&h->ev0));
-  CK(cudaEventCreate(&h->ev1));
-  CK(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device));
+  CKH(cudaEventCreate(&h->ev0));
+  CKH(cudaEventCreate(&h->ev1));
+  CKH(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device));
   const uint64_t n = n_envs;
   struct { void **p; size_t bytes; } bufs[] = {
       {(void **)&h->B.hidden, n * COG_HID_WORDS * sizeof(uint32_t)},
@@ -288,7 +304,6 @@ int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device, void 
       {(void **)&h->B.infos, n * COG_INFO_SIZE},
       {(void **)&h->B.agents, n},
       {(void **)&h->B.stats, COG_STAT_COUNT * sizeof(unsigned long long)},
-      {(void **)&h->B.err, 2 * sizeof(int)},
       {(void **)&h->B.park, 2 * sizeof(unsigned)},
   };
   for (auto &b : bufs) {
@@ -299,23 +314,35 @@ int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device, void 
       return cuda_fail(e, "cudaMalloc");
     }
   }
+  {
+    cudaError_t e = cudaHostAlloc((void **)&h->err_host, 2 * sizeof(int), cudaHostAllocMapped);
+    if (e == cudaSuccess) {
+      h->err_host[0] = h->err_host[1] = 0;
+      e = cudaHostGetDevicePointer((void **)&h->B.err, h->err_host, 0);
+    }
+    if (e != cudaSuccess) {
+      cog_vec_destroy(h);
+      return cuda_fail(e, "cudaHostAlloc (error flag)");
+    }
+  }
 #ifndef COG_EMU
-  CK(cudaFuncSetAttribute(cog::k_step_tail<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
-  CK(cudaFuncSetAttribute(cog::k_step_tail<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
-  CK(cudaFuncSetAttribute(cog::k_step_tail<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
-  CK(cudaFuncSetAttribute(cog::k_step_tail<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
+  CKH(cudaFuncSetAttribute(cog::k_step_tail<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
+  CKH(cudaFuncSetAttribute(cog::k_step_tail<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
+  CKH(cudaFuncSetAttribute(cog::k_step_tail<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
+  CKH(cudaFuncSetAttribute(cog::k_step_tail<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
   int per_sm = 0;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_fused<false, false>, cog::BLOCK_THREADS, 0));
+  CKH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_fused<false, false>, cog::BLOCK_THREADS, 0));
   h->fused_blocks_per_sm = per_sm > 0 ? per_sm : 1;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_tail<false, false>, cog::BLOCK_THREADS, scratch_bytes()));
+  CKH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_tail<false, false>, cog::BLOCK_THREADS, scratch_bytes()));
   h->tail_blocks_per_sm = per_sm > 0 ? per_sm : 1;
 #endif
   COG_LAUNCH(cog::k_init, blocks_for(n), cog::BLOCK_THREADS, 0, h->stream, h->B, n);
   g_launches++;
-  CK(cudaGetLastError());
-  CK(cudaStreamSynchronize(h->stream));
+  CKH(cudaGetLastError());
+  CKH(cudaStreamSynchronize(h->stream));
   *out = h;
   return COG_OK;
+#undef CKH
 }
 
 int cog_vec_destroy(cog_vec *h) {
@@ -323,10 +350,13 @@ int cog_vec_destroy(cog_vec *h) {
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
   void *ptrs[] = {h->B.hidden, h->B.grid, h->B.obs, h->B.masks, h->B.rewards,
-                  h->B.dones,  h->B.infos, h->B.agents, h->B.stats, h->B.err, h->B.park, h->act_staging, h->merged,
+                  h->B.dones,  h->B.infos, h->B.agents, h->B.stats, h->B.park, h->act_staging, h->merged,
                   h->compact, h->ring, h->pk_actions, h->pk_masks};
   for (void *p : ptrs)
     if (p) cudaFree(p);
+  if (h->err_host) cudaFreeHost(h->err_host);
+  if (h->ev_in) cudaEventDestroy(h->ev_in);
+  if (h->ev_order) cudaEventDestroy(h->ev_order);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   for (cudaStream_t st : h->io)
@@ -451,8 +481,7 @@ int cog_vec_read(cog_vec *h, int which, void *h_dst, size_t nbytes) {
   if (!h_dst || nbytes > item * count) return fail(COG_ERR_INVALID, "bad destination / size");
   CK(cudaSetDevice(h->device));
   CK(cudaMemcpyAsync(h_dst, p, nbytes, cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
-  return COG_OK;
+  return check_device_error(h); /* synchronises */
 }
 
 int cog_sampler_create(uint64_t n_envs, uint64_t env_index_offset, uint32_t seed, int device, void *stream,
@@ -491,6 +520,8 @@ int cog_sampler_destroy(cog_sampler *s) {
   if (s->staging) cudaFree(s->staging);
   if (s->pk_masks) cudaFree(s->pk_masks);
   if (s->pk_actions) cudaFree(s->pk_actions);
+  if (s->ev_in) cudaEventDestroy(s->ev_in);
+  if (s->ev_order) cudaEventDestroy(s->ev_order);
   for (cudaStream_t st : s->io)
     if (st) cudaStreamDestroy(st);
   for (cudaEvent_t e : s->io_ev)
@@ -515,7 +546,13 @@ int cog_sampler_sample_host(cog_sampler *s, const void *h_masks) {
   CK(cudaSetDevice(s->device));
   if (!s->staging) CK(cudaMalloc(&s->staging, s->n * COG_MASK_SIZE));
   CK(cudaMemcpyAsync(s->staging, h_masks, s->n * COG_MASK_SIZE, cudaMemcpyHostToDevice, s->stream));
-  return cog_sampler_sample(s, s->staging);
+  if (!s->ev_in) CK(cudaEventCreateWithFlags(&s->ev_in, cudaEventDisableTiming));
+  CK(cudaEventRecord(s->ev_in, s->stream));
+  const int rc = cog_sampler_sample(s, s->staging);
+  /* the caller may rewrite its array as soon as we return (the reference's sample() is synchronous with
+   * respect to its input): wait for the copy — not for the kernel, which stays asynchronous */
+  CK(cudaEventSynchronize(s->ev_in));
+  return rc;
 }
 
 int cog_sampler_actions(cog_sampler *s, void **d_ptr) {
@@ -538,7 +575,11 @@ int cog_vec_step_host(cog_vec *h, const void *h_actions) {
   const size_t bytes = h->n * COG_ACTION_SIZE;
   if (!h->act_staging) CK(cudaMalloc(&h->act_staging, bytes));
   CK(cudaMemcpyAsync(h->act_staging, h_actions, bytes, cudaMemcpyHostToDevice, h->stream));
-  return cog_vec_step(h, h->act_staging);
+  if (!h->ev_in) CK(cudaEventCreateWithFlags(&h->ev_in, cudaEventDisableTiming));
+  CK(cudaEventRecord(h->ev_in, h->stream));
+  const int rc = cog_vec_step(h, h->act_staging);
+  CK(cudaEventSynchronize(h->ev_in)); /* the caller's array is free again; the step itself stays asynchronous */
+  return rc;
 }
 
 int cog_sampler_sample_host_io(cog_sampler *s, const void *h_masks, void *h_actions_out) {
@@ -601,9 +642,9 @@ int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, v
       CK(cudaMemcpyAsync(h_rewards_out, h->B.rewards, h->n * 16, cudaMemcpyDeviceToHost, h->stream));
     if (h_dones_out) CK(cudaMemcpyAsync(h_dones_out, h->B.dones, h->n, cudaMemcpyDeviceToHost, h->stream));
     if (h_agents_out) CK(cudaMemcpyAsync(h_agents_out, h->B.agents, h->n, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
+    const int rc = check_device_error(h); /* synchronises; a failed auto-reset is reported by the call that caused it */
     if (measuring) h->tune.record(true, now_seconds() - t0);
-    return COG_OK;
+    return rc;
   }
   if (!h->act_staging) CK(cudaMalloc(&h->act_staging, h->n * COG_ACTION_SIZE));
   Pipe p{h->io, h->io_ev, h->stream};
@@ -633,7 +674,7 @@ int cog_vec_step_host_io(cog_vec *h, const void *h_actions, void *h_masks_out, v
   g_launches += (h->n + chunk - 1) / chunk;
   if (!rc) h->host_steps += h->n;
   if (measuring && !rc) h->tune.record(false, now_seconds() - t0);
-  return rc;
+  return rc ? rc : check_device_error(h);
 }
 
 /* ---- packed host I/O: 16-byte masks, 8-byte actions; staged through device memory by DMA (a 65 536-env
@@ -694,6 +735,45 @@ int cog_vec_packed_masks(cog_vec *h, void *dst, int dst_is_host, int mask_mode) 
     CK(cudaMemcpyAsync(dst, d, h->n * COGL_PACKED_MASK_SIZE, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
   }
+  return COG_OK;
+}
+
+/* ---- ordering against other streams (producers of the arrays handed to step / sample, consumers of the
+ * exported buffers): an event on the earlier stream, a wait on the later one; no host synchronisation ---- */
+namespace {
+int order_streams(int device, cudaEvent_t *ev, cudaStream_t first, cudaStream_t then) {
+  if (first == then) return COG_OK;
+  CK(cudaSetDevice(device));
+  if (!*ev) CK(cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
+  CK(cudaEventRecord(*ev, first));
+  CK(cudaStreamWaitEvent(then, *ev, 0));
+  return COG_OK;
+}
+}  // namespace
+int cog_vec_wait_stream(cog_vec *h, void *producer) {
+  if (!h) return fail(COG_ERR_INVALID, "NULL handle");
+  return order_streams(h->device, &h->ev_order, (cudaStream_t)producer, h->stream);
+}
+int cog_vec_release_to_stream(cog_vec *h, void *consumer) {
+  if (!h) return fail(COG_ERR_INVALID, "NULL handle");
+  return order_streams(h->device, &h->ev_order, h->stream, (cudaStream_t)consumer);
+}
+int cog_sampler_wait_stream(cog_sampler *s, void *producer) {
+  if (!s) return fail(COG_ERR_INVALID, "NULL handle");
+  return order_streams(s->device, &s->ev_order, (cudaStream_t)producer, s->stream);
+}
+int cog_sampler_release_to_stream(cog_sampler *s, void *consumer) {
+  if (!s) return fail(COG_ERR_INVALID, "NULL handle");
+  return order_streams(s->device, &s->ev_order, s->stream, (cudaStream_t)consumer);
+}
+int cog_vec_stream(cog_vec *h, void **stream) {
+  if (!h || !stream) return fail(COG_ERR_INVALID, "NULL argument");
+  *stream = (void *)h->stream;
+  return COG_OK;
+}
+int cog_sampler_stream(cog_sampler *s, void **stream) {
+  if (!s || !stream) return fail(COG_ERR_INVALID, "NULL argument");
+  *stream = (void *)s->stream;
   return COG_OK;
 }
 

@@ -391,6 +391,7 @@ struct Env {
   u32 Splay, Srem, Sms;
   int res[3]; /* current_resources * 2 */
   int minx, miny;
+  u32 dead; /* COG_ES_DEAD: ignore steps until reset() (finished single env / failed board generation) */
 };
 
 __device__ __forceinline__ u32 spec_of(u32 play) { return play & (COG_SPECIAL_MASK | 1u); }
@@ -438,22 +439,26 @@ __device__ __forceinline__ void env_load_scalars(Env &E, const u32 *rec, int lan
   E.lc = LANE_CONST[lane];
   const uint4 e0 = hid_vec<L2>(rec, COG_HL_ENV * 32), e1 = hid_vec<L2>(rec, COG_HL_ENV * 32 + 4);
   const uint4 e2 = hid_vec<L2>(rec, COG_HL_ENV * 32 + 8), e3 = hid_vec<L2>(rec, COG_HL_ENV * 32 + 12);
-  E.rng = e0.x;  /* COG_ES_RNG */
-  E.turn = e0.y; /* COG_ES_TURN */
-  E.agent = e0.z & 0xffu; /* COG_ES_MISC */
-  E.phase = (e0.z >> 8) & 0xffu;
-  E.n_in_market = (e0.z >> 16) & 0xffu;
-  E.res[0] = (int)e0.w; /* COG_ES_RES0.. */
-  E.res[1] = (int)e1.x;
-  E.res[2] = (int)e1.y;
-  E.minx = loc_x(e1.z); /* COG_ES_MIN */
-  E.miny = loc_y(e1.z);
-  E.Splay = e1.w; /* COG_ES_SPLAY */
-  E.Srem = e2.y;  /* COG_ES_SREM */
-  E.Sms = e2.z;   /* COG_ES_SMS */
-  E.info_steps = e2.w; /* COG_ES_INFOSTEPS */
-  E.cpf = e3.x;   /* COG_ES_CPF */
-  E.cpc = e3.y;   /* COG_ES_CPC */
+  static_assert(COG_ES_MISC == 0 && COG_ES_RES2 == 3 && COG_ES_SPLAY == 4 && COG_ES_CPC == 7 && COG_ES_RNG == 8 &&
+                    COG_ES_SREM == 11 && COG_ES_SMS == 12 && COG_ES_PENDING == 14 && COG_ES_DEAD == 15,
+                "env_load_scalars / env_store_scalars follow cog_layout.h");
+  E.agent = e0.x & 0xffu; /* COG_ES_MISC */
+  E.phase = (e0.x >> 8) & 0xffu;
+  E.n_in_market = (e0.x >> 16) & 0xffu;
+  E.res[0] = (int)e0.y; /* COG_ES_RES0.. */
+  E.res[1] = (int)e0.z;
+  E.res[2] = (int)e0.w;
+  E.Splay = e1.x;      /* COG_ES_SPLAY */
+  E.info_steps = e1.y; /* COG_ES_INFOSTEPS */
+  E.cpf = e1.z;        /* COG_ES_CPF */
+  E.cpc = e1.w;        /* COG_ES_CPC */
+  E.rng = e2.x;        /* COG_ES_RNG */
+  E.turn = e2.y;       /* COG_ES_TURN */
+  E.minx = loc_x(e2.z); /* COG_ES_MIN */
+  E.miny = loc_y(e2.z);
+  E.Srem = e2.w;       /* COG_ES_SREM */
+  E.Sms = e3.x;        /* COG_ES_SMS */
+  E.dead = e3.w;       /* COG_ES_DEAD */
 }
 /* the per-lane lines in `lines` (bit COG_HL_*) and, with bit COG_HL_PLAYER, the player line */
 template <u32 LINES, bool L2 = false>
@@ -497,6 +502,7 @@ __device__ __forceinline__ void env_uniform_scalars_hot(Env &E) { /* what every 
   E.Splay = bcast(E.Splay, 0); E.Srem = bcast(E.Srem, 0); E.Sms = bcast(E.Sms, 0);
   E.res[0] = (int)bcast((u32)E.res[0], 0); E.res[1] = (int)bcast((u32)E.res[1], 0);
   E.res[2] = (int)bcast((u32)E.res[2], 0);
+  E.dead = bcast(E.dead, 0);
 #endif
 }
 __device__ __forceinline__ void env_uniform_scalars_cold(Env &E) { /* RNG and board origin: draws, moves, resets */
@@ -510,13 +516,17 @@ __device__ __forceinline__ void env_uniform_scalars(Env &E) {
   env_uniform_scalars_cold(E);
 }
 
+/* HOT_ONLY: the first two vectors (what a card play / a phase change touches) */
+template <bool HOT_ONLY = false>
 __device__ __forceinline__ void env_store_scalars(const Env &E, u32 *rec, int lane, u32 pending = 0, u32 dead = 0) {
   if (lane == 0) {
     uint4 *ev = reinterpret_cast<uint4 *>(rec + COG_HL_ENV * 32);
-    ev[0] = make_uint4(E.rng, E.turn, E.agent | (E.phase << 8) | (E.n_in_market << 16), (u32)E.res[0]);
-    ev[1] = make_uint4((u32)E.res[1], (u32)E.res[2], loc_pack(E.minx, E.miny), E.Splay);
-    ev[2] = make_uint4(0u, E.Srem, E.Sms, E.info_steps);
-    ev[3] = make_uint4(E.cpf, E.cpc, pending, dead);
+    ev[0] = make_uint4(E.agent | (E.phase << 8) | (E.n_in_market << 16), (u32)E.res[0], (u32)E.res[1], (u32)E.res[2]);
+    ev[1] = make_uint4(E.Splay, E.info_steps, E.cpf, E.cpc);
+    if (!HOT_ONLY) {
+      ev[2] = make_uint4(E.rng, E.turn, loc_pack(E.minx, E.miny), E.Srem);
+      ev[3] = make_uint4(E.Sms, 0u, pending, dead);
+    }
   }
 }
 __device__ __forceinline__ void env_store(const Env &E, u32 *rec, int lane, u32 pending = 0, u32 dead = 0) {
@@ -547,8 +557,9 @@ __device__ __forceinline__ void export_mask(u8 *dst, u32 play, u32 spec, u32 rem
   }
 }
 
-/* everything a step can change in ObsData/ActionMask/agent_selection/Info, for
- * the players in `pmask` (bit p): phase, resources, shop stock, DeckObs[p], P[p], S */
+/* everything a step can change in ObsData/ActionMask/agent_selection/Info: phase, resources, shop
+ * stock, S, and per player p DeckObs[p] (bit p of `pmask`) and P[p] (bit 4 + p) — a turn end changes
+ * the old agent's piles and mask but only the mask of the new one */
 /* with_agent = false: vec_cog_env::reset() / reset(seed, ...) leave agent_selections[] alone — the array is
  * only written by step_single (include/vec_environment.h:33-44,53-61), so after an explicit reset it
  * still shows the agent of the last step */
@@ -564,18 +575,20 @@ __device__ __forceinline__ void export_dynamic(const Env &E, const Buffers &B, u
                    __float_as_uint(0.5f * (float)E.res[2]));
   if (lane >= 1 && lane <= 18) obs[COGL_OBS_SHOP + lane - 1] = (u8)(E.shop & 0xffu);
   for (int p = 0; p < 4; ++p) {
-    if (!((pmask >> p) & 1u)) continue;
+    if (!((pmask >> p) & 0x11u)) continue;
     u8 *pd = obs + COGL_OBS_PLAYER + COGL_PLAYER_STRIDE * p;
     const int rp = rel(E, p);
-    if (lane >= 1 && lane <= 21) {
+    if (((pmask >> p) & 1u) && lane >= 1 && lane <= 21) {
       pd[COGL_DK_DRAW + lane - 1] = (u8)getb(E.draw, rp);
       pd[COGL_DK_HAND + lane - 1] = (u8)getb(E.hand, rp);
       pd[COGL_DK_ACTIVE + lane - 1] = (u8)getb(E.active, rp);
       pd[COGL_DK_PLAYED + lane - 1] = (u8)getb(E.played, rp);
       pd[COGL_DK_DISCARD + lane - 1] = (u8)getb(E.discard, rp);
     }
-    const u32 Pplay = bcast(E.Pplay, p);
-    export_mask(pd + COGL_PD_MASK, Pplay, spec_of(Pplay), bcast(E.Prem, p), bcast(E.Pms, p), lane);
+    if ((pmask >> p) & 0x10u) {
+      const u32 Pplay = bcast(E.Pplay, p);
+      export_mask(pd + COGL_PD_MASK, Pplay, spec_of(Pplay), bcast(E.Prem, p), bcast(E.Pms, p), lane);
+    }
   }
   export_mask(B.masks + i * COGL_MASK_SIZE, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, lane);
   if (with_agent && lane == 0) B.agents[i] = (u8)E.agent;
@@ -1340,7 +1353,7 @@ __device__ __forceinline__ void env_finish_episode(Env &E, const Params &prm, co
 /* cog_env::step src/environment.cpp:91-224 followed by vec_cog_env::step_single's
  * auto-reset (include/vec_environment.h:53-61).  `act` = the five ActionData bytes
  * packed play | special<<8 | remove<<16 | move<<24, shop separately.
- * Returns: bit0 done, bits 8-11 players whose exported records changed.  When done, the
+ * Returns: bit0 done, bits 8-11 players whose DeckObs changed, bits 12-15 players whose mask changed.  When done, the
  * CALLER must run env_finish_episode() and env_reset() next (kept out of this function so
  * that each kernel holds ONE inlined copy of them — and the fused hot kernel none).
  *
@@ -1449,7 +1462,7 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop_in, const Pa
     E.cpc = pc;
   }
   const int agent = (int)E.agent;
-  u32 touched = LAZY ? 0xfu : (1u << p) | (1u << agent);
+  u32 touched = LAZY ? 0xffu : (0x11u << p) | (0x10u << agent); /* piles: bit p, masks: bit 4 + p */
   u32 done = 0;
 
   if (COG_UNLIKELY(special != SP_NONE)) { /* :183-186; src/cards.cpp:8-36; remove lambda :156-158 */
@@ -1509,7 +1522,7 @@ __device__ __forceinline__ u32 env_step(Env &E, u32 act, u32 a_shop_in, const Pa
     if (COG_UNLIKELY(finished)) {
       done = 1;
       obs_pending = false;
-      touched = 0xfu; /* the caller runs env_reset next (auto-reset, the RNG stream continues) */
+      touched = 0xffu; /* the caller runs env_reset next (auto-reset, the RNG stream continues) */
     }
   }
   return done | (touched << 8);

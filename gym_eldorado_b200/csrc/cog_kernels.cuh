@@ -47,8 +47,9 @@ __global__ void k_init(Buffers B, u64 n) {
   E.Sms = 1u | (1u << 7);
   E.res[0] = E.res[1] = E.res[2] = 0;
   E.minx = E.miny = 0;
+  E.dead = 0;
   env_store(E, B.hidden + i * COG_HID_WORDS, lane);
-  export_dynamic(E, B, i, 0xfu, lane);
+  export_dynamic(E, B, i, 0xffu, lane);
 }
 
 /* vec_cog_env<N>::reset include/vec_environment.h:33-44.  reseed: env i restarts its RNG
@@ -60,9 +61,12 @@ __global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed)
   Env E;
   env_load(E, B.hidden + i * COG_HID_WORDS, lane);
   if (reseed) E.rng = minstd_seed((u64)(u32)(seed_base + i));
-  env_reset(E, prm, B, i, warp_scratch(), lane);
-  env_store(E, B.hidden + i * COG_HID_WORDS, lane);
-  export_dynamic(E, B, i, 0xfu, lane, false);
+  const int rc = env_reset(E, prm, B, i, warp_scratch(), lane);
+  env_store(E, B.hidden + i * COG_HID_WORDS, lane, 0, rc ? 1u : 0u); /* a failed env ignores steps until a reset succeeds */
+  export_dynamic(E, B, i, 0xffu, lane, false);
+  /* the single env's own flag: cog_env::reset() clears `done` (src/environment.cpp:57); the vector env's
+   * dones[] array is only written by step_single (include/vec_environment.h:53-61) */
+  if ((prm.flags & COG_PRM_NO_AUTORESET) && lane == 0) B.dones[i] = 0;
 }
 
 /* vec_cog_env<N>::step(actions): one step per env, auto-reset included; exports only what the step
@@ -116,8 +120,6 @@ template <bool SAMPLED>
 __device__ __forceinline__ void step_one_env(const Buffers &B, const Params &prm, u64 i, const u8 *__restrict__ actions_in,
                                              u32 act_stride, u8 *masks2, u8 *pmasks, u32 *srng, u8 *actions_out, int lane) {
   u32 *rec = B.hidden + i * COG_HID_WORDS;
-  if (COG_UNLIKELY(prm.flags & COG_PRM_NO_AUTORESET)) /* dead_step src/environment.cpp:92-95 */
-    if (bcast(rec[COG_HL_ENV * 32 + COG_ES_DEAD], 0)) return;
   Env E;
   E.draw = E.played = E.discard = 0;
   E.pf = E.pc = E.pmv = E.ploc = E.Pplay = E.Prem = E.Pms = 0;
@@ -151,6 +153,10 @@ __device__ __forceinline__ void step_one_env(const Buffers &B, const Params &prm
     a_shop = a.y & 0xffu;
 #endif
   }
+  /* dead_step src/environment.cpp:92-95: a finished single env (auto-reset off) — or an env whose board
+   * generation failed — ignores steps until reset().  (In SAMPLED mode its draw is still consumed, like the
+   * reference's sampler, which knows nothing about the env.) */
+  if (COG_UNLIKELY(E.dead)) return;
   bool obs_pending = false;
   const u32 phase1 = E.phase == PH_INACTIVE ? (u32)PH_MOVEMENT : E.phase;
   const bool fast = act < 256u && !a_shop && !(E.cpf & PFL_WON) && E.turn < prm.max_steps &&
@@ -170,7 +176,8 @@ __device__ __forceinline__ void step_one_env(const Buffers &B, const Params &prm
       pd[COGL_DK_ACTIVE + lane - 1] = (u8)getb(E.active, 0);
     }
     if (lane == p) rec[COG_HL_PLAYER * 32 + COG_PF_STRIDE * lane + COG_PF_MMS] = pms;
-    env_store_scalars(E, rec, lane);
+    if (COG_LIKELY(E.Srem == Srem0)) env_store_scalars<true>(E, rec, lane); /* rng, turn, S.move / shop: untouched */
+    else env_store_scalars(E, rec, lane);
     /* export */
     if (lane == 0) {
       *reinterpret_cast<uint4 *>(obs + COGL_OBS_PHASE) =
@@ -212,8 +219,8 @@ __device__ __forceinline__ void step_one_env(const Buffers &B, const Params &prm
       if (COG_UNLIKELY(prm.flags & COG_PRM_NO_AUTORESET)) {
         env_from_absolute(E, agent, lane); /* the terminal state stays (cog_env::step does not reset) */
         dead = 1;
-      } else {
-        env_reset(E, prm, B, i, warp_scratch(), lane);
+      } else if (env_reset(E, prm, B, i, warp_scratch(), lane)) {
+        dead = 1; /* board generation failed (reported at the next synchronising call): a defined state */
       }
     }
     env_store(E, rec, lane, 0, dead);
@@ -331,6 +338,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, ROLLOUT ? (MERGED ? COG_RING_BL
     E.minx = (int)bcast((u32)E.minx, 0); E.miny = (int)bcast((u32)E.miny, 0);
     sr = bcast(sr, 0);
 #endif
+    if (COG_UNLIKELY(E.dead)) continue; /* failed board generation: ignored until reset() */
     u32 act = 0, a_shop = 0, status = 0;
     bool obs_pending = false;
     u32 k = k_steps;
@@ -354,7 +362,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, ROLLOUT ? (MERGED ? COG_RING_BL
     if (parked) {
       ++n_parked;
     } else {
-      export_dynamic(E, B, i, 0xfu, lane);
+      export_dynamic(E, B, i, 0xffu, lane);
       if (lane == 0) B.dones[i] = 0;
     }
   }
@@ -396,11 +404,15 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Bu
       t = R.t0 + j_done;
       rec = rollout_rec(R, (u32)i, slot);
     }
+    u32 dead = 0;
     for (u32 j = 0;; ++j) {
       if (status & 1u) { /* rewards / Info / aggregates, then auto-reset: the RNG stream continues */
         env_finish_episode(E, prm, B, i, lane);
         if (ROLLOUT) compact_store_rewards(rec, E, prm, lane);
-        env_reset(E, prm, B, i, sc, lane);
+        if (COG_UNLIKELY(env_reset(E, prm, B, i, sc, lane) != 0)) {
+          dead = 1; /* reported at the next synchronising call; the env ignores steps until reset() */
+          break;
+        }
       }
       if (j == k) break;
       if (ROLLOUT) {
@@ -415,8 +427,8 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Bu
     __syncwarp();
     if (lane == 0) srng[i] = sr;
     if (k) store_action(actions_out, i, act, a_shop, lane);
-    env_store(E, B.hidden + i * COG_HID_WORDS, lane);
-    export_dynamic(E, B, i, 0xfu, lane);
+    env_store(E, B.hidden + i * COG_HID_WORDS, lane, 0, dead);
+    export_dynamic(E, B, i, 0xffu, lane);
     if (lane == 0) B.dones[i] = (u8)(status & 1u);
   }
   /* park[1] can only reach park[0] once EVERY parked env was picked up, so a warp that

@@ -66,17 +66,20 @@ enum {
   COG_PF_MMS = 7,    /* P[p].move (bits 0-6) | P[p].get_from_shop (bits 7-25) */
   COG_PF_STRIDE = 8  /* words per player */
 };
-/* env scalars (line 8) */
+/* env scalars (line 8): four 16-byte vectors.  The first two hold what EVERY step changes (phase,
+ * resources, the play head of S, the step counters), the last two what only a turn end, a draw or a
+ * special action changes — the fast path of the single-step kernel writes back the first 32 bytes only */
 enum {
-  COG_ES_RNG = 0,        /* minstd_rand0 state of the env */
-  COG_ES_TURN = 1,       /* turn_counter */
-  COG_ES_MISC = 2,       /* byte0 agent_selection, byte1 phase, byte2 n_in_market */
-  COG_ES_RES0 = 3, COG_ES_RES1 = 4, COG_ES_RES2 = 5, /* current_resources * 2 (int32) */
-  COG_ES_MIN = 6,        /* int16 min_x | int16 min_y << 16 (half-hex units) */
-  COG_ES_SPLAY = 7, COG_ES_SSPEC = 8 /* unused */, COG_ES_SREM = 9, COG_ES_SMS = 10, /* S (selected mask) */
-  COG_ES_INFOSTEPS = 11, /* Info.agent_infos[k].steps_taken, one byte per player (rotated) */
-  COG_ES_CPF = 12, COG_ES_CPC = 13, /* live COG_PF_FLAGS / COG_PF_COUNTS of the current agent
-                                       (that player's words in line 7 are stale) */
+  COG_ES_MISC = 0,       /* byte0 agent_selection, byte1 phase, byte2 n_in_market */
+  COG_ES_RES0 = 1, COG_ES_RES1 = 2, COG_ES_RES2 = 3, /* current_resources * 2 (int32) */
+  COG_ES_SPLAY = 4,      /* S.play (S.play_special is derived from it) */
+  COG_ES_INFOSTEPS = 5,  /* Info.agent_infos[k].steps_taken, one byte per player (rotated) */
+  COG_ES_CPF = 6, COG_ES_CPC = 7, /* live COG_PF_FLAGS / COG_PF_COUNTS of the current agent
+                                     (that player's words in line 7 are stale) */
+  COG_ES_RNG = 8,        /* minstd_rand0 state of the env */
+  COG_ES_TURN = 9,       /* turn_counter */
+  COG_ES_MIN = 10,       /* int16 min_x | int16 min_y << 16 (half-hex units) */
+  COG_ES_SREM = 11, COG_ES_SMS = 12, /* S.remove, S.move | S.get_from_shop << 7 */
   COG_ES_PENDING = 14, /* only non-zero INSIDE a fused launch: 1 + the sample+step iterations this env
                           still owes after an episode end (k_step_tail resets the env, runs them and
                           clears the word) */

@@ -133,8 +133,9 @@ COG_API int cog_vec_set_autoreset(cog_vec *h, int on);
  * without the second launch and the mask / action round trip through memory.  (Masks from anywhere
  * else — a policy's own array, the merged masks — go through cog_sampler_sample.) */
 COG_API int cog_vec_step_sampled(cog_vec *h, cog_sampler *s);
-/* same, but `h_actions` is a HOST pointer (what the reference's step(ndarray) gets);
- * the copy is enqueued on the handle's stream */
+/* same, but `h_actions` is a HOST pointer (what the reference's step(ndarray) gets).  Returns when the
+ * array has been copied (the caller may rewrite it at once, like after the reference's synchronous
+ * step()); the step itself stays asynchronous */
 COG_API int cog_vec_step_host(cog_vec *h, const void *h_actions);
 
 /* device address of an exported buffer; stable for the handle's lifetime */
@@ -198,6 +199,21 @@ COG_API int cog_sampler_sample_packed_host_io(cog_sampler *s, const void *h_pmas
 COG_API int cog_vec_step_packed_host_io(cog_vec *h, const void *h_pactions, void *h_pmasks_out,
                                         void *h_rewards_out, void *h_dones_out, void *h_agents_out);
 COG_API int cog_vec_packed_masks(cog_vec *h, void *dst, int dst_is_host, int mask_mode);
+
+/* Streams.  Every handle enqueues on the stream it was created with; handles that exchange device buffers
+ * (the sampler's actions into cog_vec_step, the env's masks into cog_sampler_sample) must share one stream
+ * — the pybind module creates all of them on the legacy default stream — or be ordered explicitly:
+ * cog_*_wait_stream makes the handle's later work wait for what `producer` has enqueued so far (a policy
+ * network writing the action array on its own stream), cog_*_release_to_stream makes `consumer` wait for
+ * what the handle has enqueued so far (a consumer of the exported buffers: the DLPack `stream` argument).
+ * Events only, no host synchronisation.  cog_vec_run_fused(_ex) / cog_vec_step_sampled order the sampler's
+ * stream before the env's themselves. */
+COG_API int cog_vec_wait_stream(cog_vec *h, void *producer);
+COG_API int cog_vec_release_to_stream(cog_vec *h, void *consumer);
+COG_API int cog_sampler_wait_stream(cog_sampler *s, void *producer);
+COG_API int cog_sampler_release_to_stream(cog_sampler *s, void *consumer);
+COG_API int cog_vec_stream(cog_vec *h, void **stream);
+COG_API int cog_sampler_stream(cog_sampler *s, void **stream);
 
 /* Which implementation the *_host_io entry points use for PINNED arrays on these handles (either
  * may be NULL): 1 zero copy, 0 staged pipeline, -1 still measuring (fewer than nine calls so far).
