@@ -485,11 +485,18 @@ def cpu_legs(args, seconds=1.2):
     for n in (256, 65536):
         v = refshim.RefVec(n, W["seed"])
         v.reset(W["seed"], 4, 3, DIFFICULTY[W["difficulty"]], W["max_steps"])
+        # every measurement starts from a fresh reset: at N = 256 a few seconds of stepping reach max_steps, and the
+        # auto-resets that follow race on the reference's global piece tables under the threaded runner
+        fresh = lambda: v.reset(W["seed"], 4, 3, DIFFICULTY[W["difficulty"]], W["max_steps"])
         row = {"sequential": rate(lambda k: v.time_run(k, 0), n)}
         for T in sorted({t for t in (1, 2, 4, 8, 16, cores - 1) if 1 <= t <= max(1, cores - 1)}):
-            v.runner(T)
-            row["T%d" % T] = {"async": rate(lambda k: v.time_run(k, 1), n), "sync": rate(lambda k: v.time_run(k, 2), n)}
-            v.drop_runner()
+            row["T%d" % T] = {}
+            for mode, name in ((1, "async"), (2, "sync")):
+                fresh()
+                v.runner(T)
+                row["T%d" % T][name] = rate(lambda k: v.time_run(k, mode), n)
+                v.drop_runner()
+        fresh()
         if n == 65536:
             t = v.time_sample(2)
             k = max(2, int(2 * seconds / max(t, 1e-6)))

@@ -984,23 +984,6 @@ __device__ __forceinline__ int bg_add_piece(BoardScratch &sc, BoardState &st, in
   return 0;
 }
 
-/* which connection table applies (MapPiece::get_ref_connection_points src/map.cpp:203-263):
- * returns the number of entries of host->get_centered_connections(new) (0 = none).
- * first_opt = the FIRST rotation option of the table, as a value in [0, 6) */
-__device__ __forceinline__ int bg_conn_kind(int host, int newp, int &kind, int &n_alt, int &first_opt,
-                                            int &n_opts) {
-  const piece_meta h = PIECE_META[host], n = PIECE_META[newp];
-  kind = -1;
-  if (h.size == SIZE_LARGE) {
-    if (n.size == SIZE_LARGE) { kind = 0; n_alt = 2; first_opt = 4 /* -2 */; n_opts = 6; }
-    else if (n.size == SIZE_SMALL) { kind = 1; n_alt = 3; first_opt = 5 /* -1 */; n_opts = 2; }
-    else if (n.size == SIZE_TRIPLE && h.type != TYPE_START) { kind = 2; n_alt = 1; first_opt = 3 /* -3 */; n_opts = 1; }
-  } else if (h.size == SIZE_SMALL && n.size == SIZE_LARGE) {
-    kind = 3; n_alt = 6; first_opt = 4 /* -2 */; n_opts = 6;
-  }
-  if (kind < 0) return 0;
-  return kind == 3 ? n_alt : 7 * n_alt; /* base entries plus six rotated copies :249-260 */
-}
 /* rotation option `k` of a connection kind (:203-263): {-2..3}, {-1,2}, {-3}; as a value in [0, 6) */
 __device__ __forceinline__ int bg_rot_option(int kind, int k) {
   return kind == 1 ? (k == 0 ? 5 : 2) : (kind == 2 ? 3 : mod6(k + 4));
@@ -1019,9 +1002,28 @@ __device__ __forceinline__ void bg_conn_entry(int hcx, int hcy, int hrot, int ki
   y = sx8(c >> 8) + hcy;
 }
 
-/* Map::add_random_piece src/map.cpp:277-307 (+ overlap :53-74).  One round per host piece; lane e
- * tests that host's entry e (<= 21) against the occupancy bitmap: the new piece's footprint at the
- * entry's FIRST rotation option, row by row.  Returns 1 placed, 0 no candidate fits, < 0 error. */
+/* size / type of a piece from its index (the table order: 0-1 start, 2-13 large travel, 14-17 small travel,
+ * 18-19 end) — arithmetic, so that each LANE can ask about a different piece */
+__device__ __forceinline__ int piece_size(int p) { return p < 14 ? (int)SIZE_LARGE : (p < 18 ? (int)SIZE_SMALL : (int)SIZE_TRIPLE); }
+namespace tab {
+constexpr piece_meta C_META[COG_N_PIECES_TOTAL] = COG_PIECE_META_INIT;
+constexpr bool piece_order_ok() {
+  for (int p = 0; p < COG_N_PIECES_TOTAL; ++p) {
+    const int size = p < 14 ? 0 : (p < 18 ? 1 : 2), type = p < 2 ? 0 : (p < 18 ? 1 : 2);
+    if (C_META[p].size != size || C_META[p].type != type) return false;
+  }
+  return true;
+}
+}  // namespace tab
+static_assert(tab::piece_order_ok(), "piece_size() / the start-piece test follow the order of the piece table");
+
+/* Map::add_random_piece src/map.cpp:277-307 (+ overlap :53-74).  The candidates — for every piece of the
+ * map in order, the entries of its connection table towards the new piece — are numbered consecutively and
+ * tested 32 at a time, one per lane: lane c finds its host piece and entry, looks the entry's connection
+ * point up (rotations add, so one table lookup) and tests the new piece's footprint at the entry's FIRST
+ * rotation option against the occupancy bitmap, row by row.  A board of three travel pieces needs 5 rounds
+ * (14, 28, 42 and 21 candidates) where one round per host piece took 10.
+ * Returns 1 placed, 0 no candidate fits, < 0 error. */
 __device__ __forceinline__ int bg_add_random_piece(BoardScratch &sc, BoardState &st, int piece, u32 &rng,
                                                    int lane) {
   __syncwarp();
@@ -1029,45 +1031,62 @@ __device__ __forceinline__ int bg_add_random_piece(BoardScratch &sc, BoardState 
     sc.pose[piece].cx = 0; sc.pose[piece].cy = 0; sc.pose[piece].rot = 0;
   }
   __syncwarp();
-  const int shape = (int)PIECE_META[piece].size;
-  u32 my_valid = 0; /* lane k keeps the valid-entry bit set of host k */
-  int n_valid = 0;
-  for (int k = 0; k < st.n_list; ++k) {
-    const int host = (int)bcast((u32)sc.placed[k].piece, 0);
-    int kind, n_alt = 1, first_opt = 0, n_opts = 0;
-    const int n_ent = bg_conn_kind(host, piece, kind, n_alt, first_opt, n_opts);
-    if (!n_ent) continue;
-    const bg_pose hp = sc.pose[host];
-    const int hcx = (int)bcast((u32)hp.cx, 0), hcy = (int)bcast((u32)hp.cy, 0), hrot = (int)bcast((u32)hp.rot, 0);
+  const int ns = piece_size(piece);
+  /* lane k <-> piece k of the map: which connection table it offers the new piece (src/map.cpp:203-263:
+   * 0 LARGE->LARGE 14 entries, 1 LARGE->SMALL 21, 2 LARGE(not a start piece)->TRIPLE 7, 3 SMALL->LARGE 6) */
+  const int my_host = lane < st.n_list ? (int)sc.placed[lane].piece : 0;
+  const int hs = piece_size(my_host);
+  int my_kind = -1;
+  if (ns == SIZE_LARGE) my_kind = hs == SIZE_LARGE ? 0 : (hs == SIZE_SMALL ? 3 : -1);
+  else if (ns == SIZE_SMALL) my_kind = hs == SIZE_LARGE ? 1 : -1;
+  else my_kind = (hs == SIZE_LARGE && my_host >= 2) ? 2 : -1;
+  if (lane >= st.n_list) my_kind = -1;
+  const u32 my_n = my_kind < 0 ? 0u : (0x31eaeu >> (5 * my_kind)) & 31u; /* 14, 21, 7, 6 */
+  const u32 my_incl = warp_incl_scan(my_n, lane);
+  const u32 total = bcast(my_incl, 31);
+  const int n_rows = ns == SIZE_TRIPLE ? 3 : 7; /* rows of the new piece's footprint */
+  u32 my_valid = 0; /* lane r keeps the valid-candidate bit set of round r (<= 32 x 21 / 32 = 21 rounds) */
+  int n_valid = 0, round = 0;
+  for (u32 base = 0; base < total; base += 32, ++round) {
+    const u32 c = base + (u32)lane;
+    int k = 0; /* the piece of the map candidate c belongs to */
+    for (int j = 0; j < st.n_list; ++j) k += c >= bcast(my_incl, j);
+    k = k < 31 ? k : 31;
+    const int kind = max(__shfl_sync(COG_FULL, my_kind, k), 0);
+    const int e = (int)(c - (__shfl_sync(COG_FULL, my_incl, k) - __shfl_sync(COG_FULL, my_n, k)));
+    const bg_pose hp = sc.pose[__shfl_sync(COG_FULL, my_host, k)];
+    const int n_alt = (0x6132 >> (4 * kind)) & 15, first_opt = (0x4354 >> (4 * kind)) & 15; /* 2 3 1 6 / -2 -1 -3 -2 mod 6 */
     int x, y, rot_add;
-    bg_conn_entry(hcx, hcy, hrot, kind, n_alt, lane < n_ent ? lane : 0, x, y, rot_add);
-    const u32 *rows = FOOT.row[shape][mod6(first_opt + rot_add)]; /* only the FIRST rotation option is tested */
+    bg_conn_entry(hp.cx, hp.cy, hp.rot, kind, n_alt, c < total ? e : 0, x, y, rot_add);
+    const u32 *rows = FOOT.row[ns][mod6(first_opt + rot_add)]; /* only the FIRST rotation option is tested */
     u32 hit = 0;
-#pragma unroll
-    for (int j = 0; j < 7; ++j) {
-      const u32 e = rows[j];
-      const u32 X = (u32)(x + sx8(e)) & 127u, Y = (u32)(y + sx8(e >> 8)) & 127u;
+    for (int j = 0; j < n_rows; ++j) {
+      const u32 r = rows[j];
+      const u32 X = (u32)(x + sx8(r)) & 127u, Y = (u32)(y + sx8(r >> 8)) & 127u;
       const u32 w0 = Y >> 5;
       const u32 window = __funnelshift_r(sc.occ[X * 4 + w0], sc.occ[X * 4 + ((w0 + 1) & 3u)], Y & 31u);
-      hit |= window & (e >> 16);
+      hit |= window & (r >> 16);
     }
-    const u32 vm = __ballot_sync(COG_FULL, lane < n_ent && !hit);
-    if (lane == k) my_valid = vm;
+    const u32 vm = __ballot_sync(COG_FULL, c < total && !hit);
+    if (lane == round) my_valid = vm;
     n_valid += __popc(vm);
   }
   if (!n_valid) return 0;
   const u32 idx = uniform_draw(rng, (u32)n_valid);
   const u32 cnt = (u32)__popc(my_valid);
   const u32 incl = warp_incl_scan(cnt, lane);
-  const u32 hitk = __ballot_sync(COG_FULL, incl > idx);
-  const int k = __ffs((int)hitk) - 1;
-  const u32 vm = bcast(my_valid, k);
-  const u32 within = idx - (bcast(incl, k) - bcast(cnt, k));
-  const int e = (int)nth_set_bit_warp(vm, within, lane);
-  const int host = (int)bcast((u32)sc.placed[k].piece, 0);
-  int kind, n_alt = 1, first_opt = 0, n_opts = 1;
-  bg_conn_kind(host, piece, kind, n_alt, first_opt, n_opts);
+  const u32 hitr = __ballot_sync(COG_FULL, incl > idx);
+  const int r = __ffs((int)hitr) - 1;
+  const u32 vm = bcast(my_valid, r);
+  const u32 within = idx - (bcast(incl, r) - bcast(cnt, r));
+  const u32 c = 32u * (u32)r + nth_set_bit_warp(vm, within, lane); /* the chosen candidate */
+  int k = 0;
+  for (int j = 0; j < st.n_list; ++j) k += c >= bcast(my_incl, j);
+  const int kind = (int)bcast((u32)my_kind, k);
+  const int e = (int)(c - (bcast(my_incl, k) - bcast(my_n, k)));
+  const int host = (int)bcast((u32)my_host, k);
   const bg_pose hp = sc.pose[host];
+  const int n_alt = (0x6132 >> (4 * kind)) & 15, n_opts = (0x6126 >> (4 * kind)) & 15; /* rotation options: 6 2 1 6 */
   int x, y, rot_add;
   bg_conn_entry((int)bcast((u32)hp.cx, 0), (int)bcast((u32)hp.cy, 0), (int)bcast((u32)hp.rot, 0), kind, n_alt, e, x, y,
                 rot_add);
@@ -1234,14 +1253,27 @@ __device__ __forceinline__ void report_error(const Buffers &B, int code, u64 i, 
  * ActionMask::reset (include/api.h:104-118) leaves move[1..]/get_from_shop[1..] alone;
  * DeckObs::reset (:75-81) leaves `played` alone; idx_last_activated survives. */
 __device__ __forceinline__ void player_reset(Env &E, int p, int lane) {
-  u32 pc = bcast(E.pc, p) & 0xff000000u; /* n_in_hand = n_active = n_in_draw = 0 */
-  E.draw = setb(E.draw, p, 0);
-  E.hand = setb(E.hand, p, 0);
+  /* Deck::reset puts the eight starting cards (3 EXPLORER = card 0, 1 SAILOR = card 5, 4 TRAVELER = card 7) on
+   * the discard pile; the first Deck::draw moves them to the draw pile and draws four, each a uniform target
+   * below the pile size resolved by the cumulative counts in card order (src/cards.cpp:183-211).  With three
+   * card types that scan is scalar arithmetic — same draws, same result as deck_draw, a third of the
+   * instructions (the reset kernel spent a fifth of its time here). */
+  u32 left0 = 3, left5 = 1, left7 = 4, got0 = 0, got5 = 0, got7 = 0;
+  for (u32 n_in_draw = 8; n_in_draw > 4; --n_in_draw) {
+    const u32 target = uniform_draw(E.rng, n_in_draw);
+    if (target < left0) { --left0; ++got0; }
+    else if (target < left0 + left5) { --left5; ++got5; }
+    else { --left7; ++got7; }
+  }
+  E.draw = setb(E.draw, p, lane == 1 ? left0 : lane == 6 ? left5 : lane == 8 ? left7 : 0u);
+  E.hand = setb(E.hand, p, lane == 1 ? got0 : lane == 6 ? got5 : lane == 8 ? got7 : 0u);
   E.active = setb(E.active, p, 0);
-  E.discard = setb(E.discard, p, lane == 1 ? 3u : lane == 8 ? 4u : lane == 6 ? 1u : 0u);
-  E.Splay = 1u; E.Srem = 1u;
+  E.discard = setb(E.discard, p, 0);
+  E.Splay = 1u | (got0 ? 1u << 1 : 0u) | (got5 ? 1u << 6 : 0u) | (got7 ? 1u << 8 : 0u);
+  E.Srem = 1u;
   E.Sms |= 1u | (1u << 7);
-  deck_draw(E, pc, p, 4, lane);
+  /* n_in_hand = 4, n_active = 0, n_in_draw = 4; idx_last_activated survives */
+  const u32 pc = (bcast(E.pc, p) & 0xff000000u) | 4u | (4u << 16);
   if (lane == p) {
     E.pf = 0; E.pmv = 0; E.pc = pc;
     E.Pplay = E.Splay; E.Prem = E.Srem; E.Pms = E.Sms; /* save_actionmask */
@@ -1272,7 +1304,18 @@ __device__ __forceinline__ int env_reset(Env &E, const Params &prm, const Buffer
   /* Map::add_players src/map.cpp:343-354: player i stands on hex i of the start piece
    * (defined like that for fewer than 4 players too; SURVEY A#13) */
   if (lane < np) E.ploc = loc_pack(COORDS_LARGE[lane].x, COORDS_LARGE[lane].y);
-  for (int p = 0; p < np; ++p) nbr_refresh(E, grid, p, p, lane);
+  { /* the neighbour caches of all players at once: lane 8 p + d looks up direction d of player p, lane d
+     * (0..6) then collects its four bytes */
+    const int p = lane >> 3, d = lane & 7;
+    const u32 loc = __shfl_sync(COG_FULL, E.ploc, p);
+    int dx, dy;
+    dir_delta(d, dx, dy);
+    u32 code = 0;
+    if (d < 7 && p < np) code = grid_lookup(grid, loc_x(loc) + dx, loc_y(loc) + dy, E.minx, E.miny);
+    const u32 c1 = __shfl_sync(COG_FULL, code, d + 8), c2 = __shfl_sync(COG_FULL, code, d + 16),
+              c3 = __shfl_sync(COG_FULL, code, d + 24);
+    E.nbr = lane < 7 ? (code | (c1 << 8) | (c2 << 16) | (c3 << 24)) : 0u;
+  }
   /* Shop::reset src/cards.cpp:94-100 (n_in_market is NOT reset) */
   E.shop = (lane >= 1 && lane <= 18) ? (3u | (((E.lc >> 19) & 1u) << 8)) : 0u;
   E.turn = 0;
