@@ -5,15 +5,12 @@
  * stream and surfaces device-side failures.  There is no CPU implementation behind
  * this ABI: without a CUDA device every compute entry point fails with COG_ERR_CUDA.
  *
- * (tests/emu builds this same file against a lock-step warp emulator, with COG_EMU
- * defined, to check the kernels' logic on machines without a GPU; that build is test
- * infrastructure and is never loaded by the package.)
+ * (tests/emu compiles this same file with g++ against its own <cuda_runtime.h> — a lock-step
+ * warp emulator — to check the kernels' logic on machines without a GPU; that build is test
+ * infrastructure and is never loaded by the package.  The only thing this file does for it is to
+ * leave the kernel-launch statement overridable: COG_LAUNCH.)
  */
-#ifdef COG_EMU
-#include "cuda_emu.h"
-#else
 #include <cuda_runtime.h>
-#endif
 
 #include <atomic>
 #include <chrono>
@@ -27,10 +24,7 @@
 #include "cog_b200.h"
 #include "cog_kernels.cuh"
 
-#ifdef COG_EMU
-#define COG_LAUNCH(kernel, grid, block, smem, stream, ...) \
-  cuda_emu::launch((grid), (block), (smem), [&]() { kernel(__VA_ARGS__); })
-#else
+#ifndef COG_LAUNCH
 #define COG_LAUNCH(kernel, grid, block, smem, stream, ...) \
   kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
 #endif
@@ -203,10 +197,6 @@ double now_seconds() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 bool host_mapped(const void *p, void **dev) {
-#ifdef COG_EMU
-  *dev = const_cast<void *>(p); /* the emulator's "device" is host memory */
-  return true;
-#else
   cudaPointerAttributes a{};
   if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
     cudaGetLastError();
@@ -215,7 +205,6 @@ bool host_mapped(const void *p, void **dev) {
   if (a.type != cudaMemoryTypeHost || !a.devicePointer) return false;
   *dev = a.devicePointer;
   return true;
-#endif
 }
 
 uint64_t io_chunk(uint64_t n) {
@@ -244,7 +233,6 @@ template <bool MERGED, bool ROLLOUT>
 void launch_fused(cog_vec *h, cog_sampler *s, unsigned grid, unsigned tail_grid, uint32_t k_steps, const cog::Rollout &R) {
   auto hot = cog::k_step_fused<MERGED, ROLLOUT>;
   auto tail = cog::k_step_tail<MERGED, ROLLOUT>;
-#ifndef COG_EMU
   if (ROLLOUT) { /* the ring-writing kernels have their own launch bounds: fill every SM exactly once */
     static int per_sm = 0;
     if (!per_sm && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hot, cog::BLOCK_THREADS, 0) != cudaSuccess)
@@ -252,7 +240,6 @@ void launch_fused(cog_vec *h, cog_sampler *s, unsigned grid, unsigned tail_grid,
     const unsigned full = blocks_for(h->n), resident = (unsigned)(h->sm_count * (per_sm > 0 ? per_sm : 1));
     grid = full < resident ? full : resident;
   }
-#endif
   COG_LAUNCH(hot, grid, cog::BLOCK_THREADS, 0, h->stream, h->B, h->prm, h->n, s->srng, s->actions, k_steps, R);
   COG_LAUNCH(tail, tail_grid, cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm, h->n, s->srng,
              s->actions, k_steps, R);
@@ -325,7 +312,6 @@ int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device, void 
       return cuda_fail(e, "cudaHostAlloc (error flag)");
     }
   }
-#ifndef COG_EMU
   CKH(cudaFuncSetAttribute(cog::k_step_tail<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
   CKH(cudaFuncSetAttribute(cog::k_step_tail<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
   CKH(cudaFuncSetAttribute(cog::k_step_tail<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch_bytes()));
@@ -335,7 +321,6 @@ int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device, void 
   h->fused_blocks_per_sm = per_sm > 0 ? per_sm : 1;
   CKH(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cog::k_step_tail<false, false>, cog::BLOCK_THREADS, scratch_bytes()));
   h->tail_blocks_per_sm = per_sm > 0 ? per_sm : 1;
-#endif
   COG_LAUNCH(cog::k_init, blocks_for(n), cog::BLOCK_THREADS, 0, h->stream, h->B, n);
   g_launches++;
   CKH(cudaGetLastError());

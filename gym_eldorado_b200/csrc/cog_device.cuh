@@ -31,11 +31,6 @@ typedef uint64_t u64;
  * rejections) out of the hot instruction stream */
 #define COG_UNLIKELY(x) __builtin_expect(!!(x), 0)
 #define COG_LIKELY(x) __builtin_expect(!!(x), 1)
-#ifdef COG_EMU /* host build of tests/emu: libstdc++ itself spells __attribute__((__noinline__)) */
-#define COG_NOINLINE __attribute__((noinline))
-#else
-#define COG_NOINLINE __noinline__
-#endif
 
 /* ------------------------------------------------------------------ tables */
 struct card_def { u8 cost, market, single, res0, res1, res2, special; };
@@ -189,7 +184,7 @@ __device__ __forceinline__ u32 bcast(u32 v, int src) { return __shfl_sync(COG_FU
 /* inclusive prefix sum over the warp.  shfl.up reports in a predicate whether the source
  * lane exists, so every round is SHFL + one predicated IADD (no lane compares) */
 __device__ __forceinline__ u32 warp_incl_scan(u32 v, int lane) {
-#ifdef COG_EMU
+#ifndef __CUDACC__ /* a host compiler (the warp emulator of tests/emu): the same scan without PTX */
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
     u32 t = __shfl_up_sync(COG_FULL, v, d);
@@ -208,7 +203,7 @@ __device__ __forceinline__ u32 warp_incl_scan(u32 v, int lane) {
 }
 /* (a & m) | (w & ~m) as ONE LOP3 (the compiler emits two for the C expression) */
 __device__ __forceinline__ u32 bitsel(u32 a, u32 m, u32 w) {
-#ifdef COG_EMU
+#ifndef __CUDACC__
   return (a & m) | (w & ~m);
 #else
   u32 d;
@@ -417,16 +412,12 @@ __device__ __forceinline__ u32 loc_pack(int x, int y) {
  * lines that other lanes stored may still sit, stale, in this SM's L1. */
 template <bool L2 = false>
 __device__ __forceinline__ u32 hid_word(const u32 *rec, int w) {
-#ifndef COG_EMU
   if (L2) return __ldcg(rec + w);
-#endif
   return rec[w];
 }
 template <bool L2 = false>
 __device__ __forceinline__ uint4 hid_vec(const u32 *rec, int w) {
-#ifndef COG_EMU
   if (L2) return __ldcg(reinterpret_cast<const uint4 *>(rec + w));
-#endif
   return *reinterpret_cast<const uint4 *>(rec + w);
 }
 /* No shuffles: the seven per-lane lines are one coalesced load each; the player line and the

@@ -54,7 +54,10 @@ __global__ void k_init(Buffers B, u64 n) {
 
 /* vec_cog_env<N>::reset include/vec_environment.h:33-44.  reseed: env i restarts its RNG
  * from uint32(seed_base + i) (cog_env::reset(seed, ...) src/environment.cpp:66-77). */
-__global__ void k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed) {
+#ifndef COG_RESET_BLOCKS
+#define COG_RESET_BLOCKS 7
+#endif
+__global__ void __launch_bounds__(BLOCK_THREADS, COG_RESET_BLOCKS) k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed) {
   const int lane = threadIdx.x & 31;
   const u64 i = env_index(blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5));
   if (i >= n) return;

@@ -224,6 +224,8 @@ static inline unsigned __funnelshift_r(unsigned lo, unsigned hi, unsigned s) {
   return (unsigned)(((((uint64_t)hi) << 32) | lo) >> (s & 31u));
 }
 
+template <class T> static inline T __ldcg(const T *p) { return *p; } /* cache hints mean nothing here */
+
 /* lanes run one at a time, so plain read-modify-write is atomic */
 template <class T> static inline T atomicOr(T *p, T v) { T o = *p; *p = o | v; return o; }
 template <class T> static inline T atomicAdd(T *p, T v) { T o = *p; *p = o + v; return o; }
@@ -249,6 +251,20 @@ static inline cudaError_t cudaMemcpyAsync(void *d, const void *s, size_t n, cuda
 static inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
 static inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t *s, unsigned) { *s = nullptr; return cudaSuccess; }
 static inline cudaError_t cudaStreamDestroy(cudaStream_t) { return cudaSuccess; }
+/* the product's kernel-launch statement (csrc/cog_capi.cu: COG_LAUNCH), overridden: blocks and warps run one
+ * after the other on the calling thread */
+#define COG_LAUNCH(kernel, grid, block, smem, stream, ...) \
+  cuda_emu::launch((grid), (block), (smem), [&]() { kernel(__VA_ARGS__); })
+/* "device" memory is host memory: every pointer is device addressable */
+enum cudaMemoryType { cudaMemoryTypeUnregistered = 0, cudaMemoryTypeHost = 1, cudaMemoryTypeDevice = 2 };
+struct cudaPointerAttributes { cudaMemoryType type; int device; void *devicePointer; void *hostPointer; };
+static inline cudaError_t cudaPointerGetAttributes(cudaPointerAttributes *a, const void *p) {
+  a->type = cudaMemoryTypeHost; a->device = 0; a->devicePointer = a->hostPointer = const_cast<void *>(p);
+  return cudaSuccess;
+}
+enum { cudaFuncAttributeMaxDynamicSharedMemorySize = 8 };
+template <class F> static inline cudaError_t cudaFuncSetAttribute(F, int, int) { return cudaSuccess; }
+template <class F> static inline cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int *n, F, int, size_t) { *n = 1; return cudaSuccess; }
 enum { cudaHostAllocMapped = 2, cudaEventDisableTiming = 2 };
 static inline cudaError_t cudaHostAlloc(void **p, size_t n, unsigned) { *p = std::malloc(n ? n : 1); return *p ? cudaSuccess : 2; }
 static inline cudaError_t cudaFreeHost(void *p) { std::free(p); return cudaSuccess; }
