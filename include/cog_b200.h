@@ -224,6 +224,12 @@ COG_API int cog_io_path(cog_vec *h, cog_sampler *s, int *vec_path, int *sampler_
  * { sample(selected_action_masks); step(actions) } in ONE persistent kernel with
  * no host round trip; bit-identical to k_steps single sample+step calls.
  * The sampler's action buffer holds the last sampled actions afterwards. */
+/* What the exported buffers show afterwards is the state after the LAST of the k steps: `dones` holds the
+ * done flags of that step only (an env whose episode ended earlier in the launch has been auto-reset and
+ * stepped on, like in the reference's loop, where the caller would have seen dones[i] == true on that step
+ * and here does not), `rewards` / `infos` keep the values of each env's most recent episode end, and
+ * cog_vec_stats counts every episode.  A caller that needs per-step dones / rewards attaches a rollout ring
+ * (cog_vec_rollout_attach: one record per env-step, done and rewards included) or steps with k_steps = 1. */
 COG_API int cog_vec_run_fused(cog_vec *h, cog_sampler *s, uint64_t k_steps);
 
 /* Which mask the fused loop samples from.  The reference keeps the legal actions of the
