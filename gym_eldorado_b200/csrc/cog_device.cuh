@@ -1613,17 +1613,68 @@ __device__ __forceinline__ bool minstd_skip4_unit_draws(u32 &s) {
   return true;
 }
 
+/* ---- all five heads at once (the general case: several heads have a choice) -----------------------
+ * Draw k of a sample() call consumes engine output k + 1 as long as no earlier draw was rejected, and
+ * output k + 1 is x a^(k+1) mod m: lane k (0..4) computes ITS output with one modular multiply by a
+ * per-lane constant, takes its own head's table entry, and finds its own n-th set bit; one OR-reduction
+ * and two shuffles collect the five indices.  A rejected draw in any lane (a few in 2^31) — or an empty
+ * head — leaves the state untouched and returns false: the caller takes the step-by-step path. */
+namespace tab {
+constexpr u32 minstd_pow(int k) { /* 16807^k mod (2^31 - 1) */
+  u64 v = 1;
+  for (int i = 0; i < k; ++i) v = v * 16807ull % 2147483647ull;
+  return (u32)v;
+}
+}  // namespace tab
+__device__ const u32 MINSTD_POW_LANE[32] = {
+    tab::minstd_pow(1), tab::minstd_pow(2), tab::minstd_pow(3), tab::minstd_pow(4), tab::minstd_pow(5),
+    1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1};
+static_assert(tab::minstd_pow(4) == 984943658u && tab::minstd_pow(5) == 1144108930u, "powers of the minstd multiplier");
+/* the same table as UD_TAB for per-LANE indices (constant memory serialises divergent addresses) */
+__device__ const ud_entry UD_TAB_LANE[33] = {
+    COG_UD(0),  COG_UD(1),  COG_UD(2),  COG_UD(3),  COG_UD(4),  COG_UD(5),  COG_UD(6),  COG_UD(7),  COG_UD(8),
+    COG_UD(9),  COG_UD(10), COG_UD(11), COG_UD(12), COG_UD(13), COG_UD(14), COG_UD(15), COG_UD(16), COG_UD(17),
+    COG_UD(18), COG_UD(19), COG_UD(20), COG_UD(21), COG_UD(22), COG_UD(23), COG_UD(24), COG_UD(25), COG_UD(26),
+    COG_UD(27), COG_UD(28), COG_UD(29), COG_UD(30), COG_UD(31), COG_UD(32)};
+
+__device__ __forceinline__ bool sample_heads_parallel(u32 &rng, u32 play, u32 spec, u32 rem, u32 ms, u32 &act,
+                                                      u32 &a_shop, int lane) {
+  const u32 head = lane == 0 ? play : (lane == 1 ? spec : (lane == 2 ? rem : (lane == 3 ? (ms & 0x7fu) : (ms >> 7))));
+  const u32 n = (u32)__popc(head); /* <= 22 */
+  const u64 t = (u64)rng * MINSTD_POW_LANE[lane];   /* < 2^62 */
+  const u64 f = (t & 0x7fffffffull) + (t >> 31);    /* < 2^32 */
+  u32 o = (u32)(f & 0x7fffffffull) + (u32)(f >> 31);
+  if (o >= 0x7fffffffu) o -= 0x7fffffffu;
+  const u32 r = o - 1u;
+  const ud_entry e = UD_TAB_LANE[n]; /* n == 0: past = 0, every r is "rejected" */
+  if (COG_UNLIKELY(__any_sync(COG_FULL, lane < 5 && r >= e.past))) return false;
+  u32 v = head;
+  for (u32 j = ud_quotient(r, e); j; --j) v &= v - 1u; /* the j-th set bit of this lane's head */
+  const u32 idx = (u32)__ffs((int)v) - 1u;
+  act = __reduce_or_sync(COG_FULL, lane < 4 ? idx << (8 * lane) : 0u);
+  a_shop = bcast(idx, 4);
+  rng = bcast(o, 4);
+  return true;
+}
+
 /* The heads are bit sets with nothing above bit 21 (play, special, remove) / bit 25 (ms =
  * move | get_from_shop << 7): every producer builds them from lane-guarded ballots. */
 /* Returns true when only the `play` head had a choice (act < 256, a_shop = 0). */
 __device__ __forceinline__ bool sample_action(u32 &rng, u32 play, u32 spec, u32 rem, u32 ms, u32 &act,
                                               u32 &a_shop, int lane) {
-  const u32 a0 = sample_head_warp(rng, play, lane);
-  if (spec == 1u && rem == 1u && ms == 0x81u && minstd_skip4_unit_draws(rng)) {
-    a_shop = 0; /* the reference's own flow: only `play` ever has a choice (SURVEY A#2) */
-    act = a0;
-    return true;
+  u32 a0;
+  if (spec == 1u && rem == 1u && ms == 0x81u) { /* the reference's own flow: only `play` ever has a choice (SURVEY A#2) */
+    a0 = sample_head_warp(rng, play, lane);
+    if (COG_LIKELY(minstd_skip4_unit_draws(rng))) {
+      a_shop = 0;
+      act = a0;
+      return true;
+    }
+  } else {
+    if (COG_LIKELY(sample_heads_parallel(rng, play, spec, rem, ms, act, a_shop, lane))) return false;
+    a0 = sample_head(rng, play);
   }
+  /* step by step: a draw was rejected somewhere (or a head is empty) */
   const u32 mv = ms & 0x7fu, shop = ms >> 7;
   const u32 a1 = sample_head(rng, spec);
   const u32 a2 = sample_head(rng, rem);

@@ -285,7 +285,12 @@ __device__ __forceinline__ u32 sample_and_step(Env &E, u32 &sr, u32 &act, u32 &a
     merged_heads(E, lane, rem, ms);
     sample_action(sr, E.Splay, spec_of(E.Splay), rem, ms, act, a_shop, lane);
     if (ROLLOUT) compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), rem, ms, act, a_shop, t, lane);
-    status = env_step<false, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
+    /* most steps are still card plays and nulls: they take the instantiation whose other branches fold away */
+#ifndef COG_NO_M_DISPATCH
+    if (act < 256u && !a_shop) status = env_step<false, true>(E, act, 0u, prm, B, i, obs_pending, lane);
+    else
+#endif
+      status = env_step<false, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
   } else {
     const bool play_only = sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane);
     if (ROLLOUT) compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, t, lane);

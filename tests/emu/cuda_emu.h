@@ -59,7 +59,7 @@ __asm__(
 namespace cuda_emu {
 
 enum Op { OP_NONE = 0, OP_SYNC, OP_SHFL, OP_SHFL_UP, OP_SHFL_XOR, OP_BALLOT, OP_ANY, OP_ALL,
-          OP_RED_ADD, OP_RED_MIN_S, OP_RED_MAX_S, OP_RED_MIN_U, OP_RED_MAX_U };
+          OP_RED_ADD, OP_RED_MIN_S, OP_RED_MAX_S, OP_RED_MIN_U, OP_RED_MAX_U, OP_RED_OR };
 
 struct Fiber { void *sp = nullptr; bool done = true; char *stack = nullptr; int op = OP_NONE; };
 constexpr size_t STACK_BYTES = 512 * 1024;
@@ -105,6 +105,8 @@ static void resolve(int op) {
     for (int l = 0; l < 32; ++l) g_out[l] = acc;
     break;
   case OP_RED_ADD: for (int l = 0; l < 32; ++l) acc += g_in[l];
+    for (int l = 0; l < 32; ++l) g_out[l] = acc; break;
+  case OP_RED_OR: for (int l = 0; l < 32; ++l) acc |= g_in[l];
     for (int l = 0; l < 32; ++l) g_out[l] = acc; break;
   case OP_RED_MIN_S: case OP_RED_MAX_S: {
     int32_t v = (int32_t)g_in[0];
@@ -193,6 +195,7 @@ static inline int __any_sync(unsigned, int pred) { return (int)cuda_emu::collect
 static inline int __all_sync(unsigned, int pred) { return (int)cuda_emu::collective(cuda_emu::OP_ALL, pred != 0, 0); }
 static inline unsigned __reduce_add_sync(unsigned, unsigned v) { return cuda_emu::collective(cuda_emu::OP_RED_ADD, v, 0); }
 static inline int __reduce_add_sync(unsigned, int v) { return (int)cuda_emu::collective(cuda_emu::OP_RED_ADD, (uint32_t)v, 0); }
+static inline unsigned __reduce_or_sync(unsigned, unsigned v) { return cuda_emu::collective(cuda_emu::OP_RED_OR, v, 0); }
 static inline int __reduce_min_sync(unsigned, int v) { return (int)cuda_emu::collective(cuda_emu::OP_RED_MIN_S, (uint32_t)v, 0); }
 static inline int __reduce_max_sync(unsigned, int v) { return (int)cuda_emu::collective(cuda_emu::OP_RED_MAX_S, (uint32_t)v, 0); }
 static inline unsigned __reduce_min_sync(unsigned, unsigned v) { return cuda_emu::collective(cuda_emu::OP_RED_MIN_U, v, 0); }
