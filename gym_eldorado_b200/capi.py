@@ -15,6 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libcog_b200.so")
 
 COG_OK = 0
+NOALLOC_MAX_ENVS = 65536  # COG_NOALLOC_MAX_ENVS (include/cog_b200.h)
 COG_ERR_INVALID, COG_ERR_MAP_FAILURE, COG_ERR_MAP_BOUNDS, COG_ERR_CUDA, COG_ERR_NOT_RESET = -1, -2, -3, -4, -5
 STAT_NAMES = ("env_steps", "episodes", "truncations", "total_length", "wins_seat0", "wins_seat1",
               "wins_seat2", "wins_seat3", "travelled_hexes", "cards_added", "resets", "reserved")
@@ -53,6 +54,7 @@ SYMBOLS = {
     "cog_vec_stream": (_int, [_vp, _P(_vp)]),
     "cog_sampler_stream": (_int, [_vp, _P(_vp)]),
     "cog_sampler_sample_packed_host_io": (_int, [_vp, _vp, _vp]),
+    "cog_sampler_sample_packed_noalloc": (_int, [_vp, _vp, _vp]),
     "cog_vec_step_packed_host_io": (_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "cog_vec_packed_masks": (_int, [_vp, _vp, _int, _int]),
     "cog_vec_run_fused": (_int, [_vp, _vp, _u64]),
@@ -287,6 +289,13 @@ class SamplerHandle:
         assert pmasks.dtype == layout.packed_mask_dtype and pmasks.flags.c_contiguous and len(pmasks) == self.n
         assert pactions_out.dtype == layout.packed_action_dtype and len(pactions_out) == self.n
         check(self.L, self.L.cog_sampler_sample_packed_host_io(self._s, pmasks.ctypes.data, pactions_out.ctypes.data))
+
+    def sample_packed_noalloc(self, pmasks, pactions_out):
+        """sample_packed_host_io through the library's static device scratch: the call allocates nothing
+        (at most NOALLOC_MAX_ENVS envs; all calls on a device share the scratch)"""
+        assert pmasks.dtype == layout.packed_mask_dtype and pmasks.flags.c_contiguous and len(pmasks) == self.n
+        assert pactions_out.dtype == layout.packed_action_dtype and len(pactions_out) == self.n
+        check(self.L, self.L.cog_sampler_sample_packed_noalloc(self._s, pmasks.ctypes.data, pactions_out.ctypes.data))
 
     def actions_ptr(self):
         p = _vp()

@@ -679,6 +679,58 @@ int cog_sampler_sample_packed_host_io(cog_sampler *s, const void *h_pmasks, void
   return COG_OK;
 }
 
+/* ---- the no-allocation variant of the call above (no counterpart in the reference; see cog_b200.h) ----
+ * Staging for the packed masks (first part) and the packed actions (second part) of up to
+ * COG_NOALLOC_MAX_ENVS envs.  One array per device that loads this library; every call on that device
+ * shares it.  In HOST code the name below is only a handle for cudaGetSymbolAddress — never a pointer a
+ * kernel may be given. */
+namespace {
+enum : size_t {
+  NOALLOC_MASK_BYTES = (size_t)COG_NOALLOC_MAX_ENVS * COGL_PACKED_MASK_SIZE,
+  NOALLOC_ACTION_BYTES = (size_t)COG_NOALLOC_MAX_ENVS * COGL_PACKED_ACTION_SIZE,
+  NOALLOC_MAX_DEVICES = 64
+};
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_MASK_BYTES + NOALLOC_ACTION_BYTES];
+std::atomic<unsigned char *> g_noalloc_addr[NOALLOC_MAX_DEVICES];
+
+/* device address of the array on `device` (which must be current); resolved once per device */
+int noalloc_scratch(int device, unsigned char **out) {
+  if (device < 0 || device >= (int)NOALLOC_MAX_DEVICES) return fail(COG_ERR_INVALID, "device ordinal out of range");
+  unsigned char *p = g_noalloc_addr[device].load(std::memory_order_acquire);
+  if (!p) {
+    void *sym = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&sym, g_noalloc_scratch);
+    if (e != cudaSuccess || !sym) return cuda_fail(e, "cudaGetSymbolAddress(no-alloc scratch)");
+    p = (unsigned char *)sym;
+    g_noalloc_addr[device].store(p, std::memory_order_release); /* racing threads resolve the same address */
+  }
+  *out = p;
+  return COG_OK;
+}
+}  // namespace
+
+int cog_sampler_sample_packed_noalloc(cog_sampler *s, const void *h_pmasks, void *h_pactions_out) {
+  if (!s || !h_pmasks || !h_pactions_out) return fail(COG_ERR_INVALID, "NULL argument");
+  if (s->n > (uint64_t)COG_NOALLOC_MAX_ENVS)
+    return fail(COG_ERR_INVALID, "cog_sampler_sample_packed_noalloc: sampler has " + std::to_string(s->n) +
+                                     " envs, the static scratch holds at most COG_NOALLOC_MAX_ENVS = " +
+                                     std::to_string((uint64_t)COG_NOALLOC_MAX_ENVS) +
+                                     " (use cog_sampler_sample_packed_host_io, or shard the sampler)");
+  CK(cudaSetDevice(s->device));
+  unsigned char *scratch = nullptr;
+  const int rc = noalloc_scratch(s->device, &scratch);
+  if (rc) return rc;
+  unsigned char *d_masks = scratch, *d_actions = scratch + NOALLOC_MASK_BYTES;
+  CK(cudaMemcpyAsync(d_masks, h_pmasks, s->n * COGL_PACKED_MASK_SIZE, cudaMemcpyHostToDevice, s->stream));
+  COG_LAUNCH(cog::k_sample<true>, blocks_for(s->n), cog::BLOCK_THREADS, 0, s->stream, (const uint8_t *)d_masks,
+             s->srng, s->actions, s->n, (uint8_t *)d_actions);
+  g_launches++;
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(h_pactions_out, d_actions, s->n * COGL_PACKED_ACTION_SIZE, cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream)); /* the host array is complete, and the shared scratch free, on return */
+  return COG_OK;
+}
+
 int cog_vec_step_packed_host_io(cog_vec *h, const void *h_pactions, void *h_pmasks_out, void *h_rewards_out,
                                 void *h_dones_out, void *h_agents_out) {
   if (!h || !h_pactions) return fail(COG_ERR_INVALID, "NULL argument");

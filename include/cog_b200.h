@@ -200,6 +200,30 @@ COG_API int cog_vec_step_packed_host_io(cog_vec *h, const void *h_pactions, void
                                         void *h_rewards_out, void *h_dones_out, void *h_agents_out);
 COG_API int cog_vec_packed_masks(cog_vec *h, void *dst, int dst_is_host, int mask_mode);
 
+/* cog_sampler_sample_packed_noalloc — NO COUNTERPART IN THE REFERENCE; added
+ * for callers that must not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).
+ *
+ * The same operation, argument meaning and results as cog_sampler_sample_packed_host_io above (bit-identical
+ * packed actions, the same advance of the sampler's RNG streams, the sampler's ActionData buffer updated), but
+ * the device staging of the packed masks and packed actions is NOT allocated on first use: it lives in a
+ * file-scope `static __device__ __align__(256)` array inside the library
+ *   COG_NOALLOC_MAX_ENVS * (COG_PACKED_MASK_SIZE + COG_PACKED_ACTION_SIZE) = 65 536 * 24 bytes = 1.5 MiB
+ * that every GPU which loads the library holds until the process exits.  The call performs no cudaMalloc,
+ * cudaFree, event / stream creation or any other allocating runtime or library routine (the array's device
+ * address is resolved once per device with cudaGetSymbolAddress — that device current, return code checked —
+ * on the first call made for that device, and cached).
+ *   - a sampler of more than COG_NOALLOC_MAX_ENVS envs is rejected with COG_ERR_INVALID and a message that
+ *     names the limit (cog_last_error); nothing is launched.
+ *   - ALL calls on one device share the one array, whichever sampler or stream they use: two calls whose GPU
+ *     work overlaps (different streams, different host threads) RACE on it.  The call returns after its stream
+ *     has drained, so calls issued one after the other from one thread are safe.
+ *   - the array keeps the previous call's contents; nothing in it has to start at zero (the first n_envs packed
+ *     masks are overwritten by the host-to-device copy and all 8 bytes of each of the first n_envs packed
+ *     actions by the kernel before they are copied out), bytes beyond n_envs are never read. */
+#define COG_NOALLOC_MAX_ENVS 65536
+COG_API int cog_sampler_sample_packed_noalloc(cog_sampler *s, const void *h_pmasks, void *h_pactions_out);
+
 /* Streams.  Every handle enqueues on the stream it was created with; handles that exchange device buffers
  * (the sampler's actions into cog_vec_step, the env's masks into cog_sampler_sample) must share one stream
  * — the pybind module creates all of them on the legacy default stream — or be ordered explicitly:

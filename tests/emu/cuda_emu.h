@@ -30,6 +30,7 @@
 #define __shared__
 #define __constant__
 #define __launch_bounds__(...)
+#define __align__(n) __attribute__((aligned(n)))
 
 using std::max;
 using std::min;
@@ -265,6 +266,8 @@ static inline cudaError_t cudaPointerGetAttributes(cudaPointerAttributes *a, con
   a->type = cudaMemoryTypeHost; a->device = 0; a->devicePointer = a->hostPointer = const_cast<void *>(p);
   return cudaSuccess;
 }
+/* a `__device__` array is plain host memory here: its address is the symbol's address */
+template <class T> static inline cudaError_t cudaGetSymbolAddress(void **p, const T &symbol) { *p = const_cast<void *>(static_cast<const void *>(&symbol)); return cudaSuccess; }
 enum { cudaFuncAttributeMaxDynamicSharedMemorySize = 8 };
 template <class F> static inline cudaError_t cudaFuncSetAttribute(F, int, int) { return cudaSuccess; }
 template <class F> static inline cudaError_t cudaOccupancyMaxActiveBlocksPerMultiprocessor(int *n, F, int, size_t) { *n = 1; return cudaSuccess; }
