@@ -33,8 +33,8 @@ import bench_parts as bp  # noqa: E402
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--inner", type=int, default=1024, help="fused sample+step iterations per launch")
     ap.add_argument("--config", type=int, default=2, choices=sorted(bp.WORKLOADS), help="BASELINE.json configs index")
@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cpu-legs", action="store_true", help="skip the thread sweep / reset / sample CPU legs")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-clocks", action="store_true", help="do not poll nvidia-smi during the timed region (diagnosis)")
     ap.add_argument("--no-resets", action="store_true")
     ap.add_argument("--no-side", action="store_true", help="skip the regime-M / reset-heavy / API-loop side measurements")
     ap.add_argument("--no-config4", action="store_true", help="skip the configs[4] leg of a multi-GPU run")
@@ -55,13 +56,18 @@ def parse():
 
 def main():
     args = parse()
+    # ONE line on stdout: whatever libraries print there while the job runs (NCCL's version banner under
+    # torchrun, for one) goes to stderr; the JSON line is written to the real stdout at the end
+    sys.stdout.flush()
+    out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
 
     if args.impl == "reference":
         if rank == 0:
-            print(json.dumps(bp.reference_arm(args, world)))
+            print(json.dumps(bp.reference_arm(args, world)), file=out, flush=True)
         return
 
     import torch
@@ -86,12 +92,13 @@ def main():
     launches0 = L.cog_kernel_launches()
 
     # ---- the timed region: K launches of the fused kernel --------------------------------------
+    clocks = bp.ClockSampler(local_rank)  # attaches to NVML and starts polling now, well before the timed region
+    if rank == 0 and not args.no_clocks:
+        clocks.start()
     for _ in range(args.warmup):
         vec.run_fused(smp, args.inner)
     ctx.barrier()
-    clocks = bp.ClockSampler(local_rank)
-    if rank == 0:
-        clocks.start()
+    clocks.mark_begin()
     vec.stats_reset()
     launches_timed0 = L.cog_kernel_launches()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -103,7 +110,7 @@ def main():
     ev1.record()
     ctx.barrier()
     ms = ctx.max_over_ranks(ev0.elapsed_time(ev1))
-    clk = clocks.finish() if rank == 0 else None
+    clk = clocks.finish() if rank == 0 and not args.no_clocks else None
     launches_timed = L.cog_kernel_launches() - launches_timed0
     assert stats["env_steps"] == world * n * args.inner * args.steps, "work was skipped"
     value = stats["env_steps"] / (ms * 1e-3)
@@ -152,7 +159,7 @@ def main():
                 "note": "headline = regime A, the reference's own README / pytest / asv flow (actions sampled from "
                         "selected_action_masks: only play / null ever occur, %d episodes finished in the timed region); "
                         "regime_M = the same kernels with every branch of step live" % stats["episodes"]}
-        print(json.dumps(line))
+        print(json.dumps(line), file=out, flush=True)
     vec.close()
     smp.close()
     if world > 1:

@@ -75,42 +75,73 @@ def issue_frac(units_per_s_per_gpu, warp_inst_per_unit, sm_mhz):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks/throttle reasons DURING the timed region (profiling recipe)."""
+    """SM clock and throttle reasons DURING the timed region (profiling recipe's clocks line).  Read through
+    NVML inside this process (one nvmlInit before the timed region, then two cheap queries every 20 ms): a
+    fresh `nvidia-smi` process per sample attaches to the driver each time and stalls the GPU for 8-15 ms —
+    measured here as 5.23e9 env-steps/s without sampling against 4.5-5.2e9 with it (gpurun_out/r02_o.txt).
+    Falls back to nvidia-smi (one sample every 0.5 s) when NVML cannot be loaded."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.rows, self._halt = index, [], threading.Event()
+        self.t_begin = 0.0  # samples taken before mark_begin() (warm-up) are dropped
+        self.nvml, self.handle, self.source = None, None, "nvidia-smi"
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            p = torch.cuda.get_device_properties(index)
+            bus = "%08x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+            self.handle = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml, self.source = pynvml, "nvml"
+            self._sample_nvml()  # the first query of a process is the slow one
+        except Exception:
+            self.nvml = None
+
+    def _sample_nvml(self):
+        n = self.nvml
+        mhz = float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM))
+        bits = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+        flags = [bool(bits & n.nvmlClocksThrottleReasonHwSlowdown), bool(bits & n.nvmlClocksThrottleReasonHwThermalSlowdown),
+                 bool(bits & n.nvmlClocksThrottleReasonSwThermalSlowdown), bool(bits & n.nvmlClocksThrottleReasonSwPowerCap)]
+        return [mhz, self.max_mhz] + flags
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                              "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+        r = [x.strip() for x in out.strip().split(",")]
+        return [float(r[0]), float(r[1])] + [v.lower().startswith("active") for v in r[2:6]]
 
     def run(self):
         while not self._halt.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([x.strip() for x in out.strip().split(",")])
+                t = time.perf_counter()
+                self.rows.append((t, self._sample_nvml() if self.nvml else self._sample_smi()))
             except Exception:
                 pass
-            self._halt.wait(0.1)
+            self._halt.wait(0.02 if self.nvml else 0.5)
+
+    def mark_begin(self):
+        """the timed region starts now (the thread has been polling since before the warm-up, so that its
+        start-up and NVML's first queries fall outside the region)"""
+        self.t_begin = time.perf_counter()
 
     def finish(self):
         self._halt.set()
         self.join(timeout=6)
         sm, mx, reasons = [], 0.0, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            if len(r) < 6:
+        for t, r in self.rows:
+            if t < self.t_begin:
                 continue
-            try:
-                sm.append(float(r[0])); mx = max(mx, float(r[1]))
-            except ValueError:
-                continue
-            for name, v in zip(names, r[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
+            sm.append(r[0]); mx = max(mx, r[1])
+            reasons.update(name for name, on in zip(self.NAMES, r[2:6]) if on)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": self.source}
 
 
 class Ctx:
@@ -332,10 +363,12 @@ def measure_e2e(ctx, L, vec, smp, n, steps):
     from gym_eldorado_b200 import layout
     mdt, adt = layout.action_mask_dtype, layout.action_dtype
     pm_dt, pa_dt = layout.packed_mask_dtype, layout.packed_action_dtype
-    h_masks, h_actions = _pinned(n * mdt.itemsize), _pinned(n * adt.itemsize)
-    h_pm, h_pa = _pinned(n * pm_dt.itemsize), _pinned(n * pa_dt.itemsize)
-    h_rew, h_done, h_agent = _pinned(n * 16), _pinned(n), _pinned(n)
-    h_compact = _pinned(n * layout.compact_dtype.itemsize)
+    from gym_eldorado_b200 import shard
+    with shard.near_gpu(ctx.local_rank) as numa:  # the rank's host arrays on the NUMA node of its GPU
+        h_masks, h_actions = _pinned(n * mdt.itemsize), _pinned(n * adt.itemsize)
+        h_pm, h_pa = _pinned(n * pm_dt.itemsize), _pinned(n * pa_dt.itemsize)
+        h_rew, h_done, h_agent = _pinned(n * 16), _pinned(n), _pinned(n)
+        h_compact = _pinned(n * layout.compact_dtype.itemsize)
     np_masks, np_actions = h_masks.numpy().view(mdt), h_actions.numpy().view(adt)
     np_pm, np_pa = h_pm.numpy().view(pm_dt), h_pa.numpy().view(pa_dt)
     np_rew = h_rew.numpy().view(np.float32).reshape(n, 4)
@@ -404,6 +437,7 @@ def measure_e2e(ctx, L, vec, smp, n, steps):
                                                 "dma": {"h2d": full, "d2h": full + n * 18}},
             "zero_copy_value": zero, "dma_pipeline_value": piped, "serial_calls_value": serial,
             "host_memcpy_GBs": host_memcpy_gbs() if ctx.rank == 0 else None,
+            "host_arrays_numa": numa.info,
             "note": "value = packed records (opt-in entry points: the same information as the reference's ActionMask / "
                     "ActionData in 16 + 8 bytes); reference_layout_value = the reference's own record layouts through "
                     "cog_sampler_sample_host_io / cog_vec_step_host_io (path auto-selected per handle: "
@@ -524,7 +558,9 @@ def reference_arm(args, world):
     same config / metric / unit; each step a bounded sample of the workload."""
     v, kind, n, used, run, how = _ref_runner(args)
     t = run(2)
-    ref_inner = max(1, int(2 * 1.0 / max(t, 1e-6)))  # about one second per step
+    # about one second per step, less when many steps are asked for: the whole run stays near 30 s
+    per_step_s = max(0.2, min(1.0, 30.0 / max(1, args.steps + args.warmup)))
+    ref_inner = max(1, int(2 * per_step_s / max(t, 1e-6)))
     for _ in range(args.warmup):
         run(ref_inner)
     t0 = time.perf_counter()

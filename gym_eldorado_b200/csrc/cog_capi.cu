@@ -27,6 +27,25 @@
 #ifndef COG_LAUNCH
 #define COG_LAUNCH(kernel, grid, block, smem, stream, ...) \
   kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__)
+/* programmatic dependent launch: the grid may become resident while the previous kernel of the stream
+ * drains; the kernel itself waits (griddepcontrol.wait) before it touches memory */
+template <class... P, class... A>
+static void cog_launch_pdl(void (*kernel)(P...), unsigned grid, unsigned block, size_t smem, cudaStream_t stream, A... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, kernel, P(args)...);
+}
+#define COG_LAUNCH_PDL(kernel, grid, block, smem, stream, ...) cog_launch_pdl(kernel, grid, block, smem, stream, __VA_ARGS__)
+#else
+#define COG_LAUNCH_PDL COG_LAUNCH
 #endif
 
 static_assert(COG_OBS_SIZE == COGL_OBS_SIZE && COG_MASK_SIZE == COGL_MASK_SIZE &&
@@ -140,6 +159,18 @@ void time_end(cog_vec *h) {
   cudaEventRecord(h->ev1, h->stream);
   h->timed = true;
 }
+/* Single steps are NOT bracketed by timing events unless COG_STEP_EVENTS=1: a timing event between two
+ * kernels of a stream is a full serialisation point (measured: 44.0 us per sample+step of 65 536 envs with
+ * the events, 38.9 us without, 36.5 us with programmatic dependent launch on top — gpurun_out/r02_l). */
+bool step_events() {
+  static const bool on = std::getenv("COG_STEP_EVENTS") && std::atoi(std::getenv("COG_STEP_EVENTS")) != 0;
+  return on;
+}
+/* programmatic dependent launch of the per-step kernels (COG_PDL=0 turns it off) */
+bool use_pdl() {
+  static const bool on = !(std::getenv("COG_PDL") && std::atoi(std::getenv("COG_PDL")) == 0);
+  return on;
+}
 
 int launch_reset(cog_vec *h, uint32_t seed, int reseed) {
   CK(cudaSetDevice(h->device));
@@ -225,6 +256,11 @@ namespace {
 template <bool SAMPLED>
 void launch_single(cog_vec *h, cudaStream_t stream, uint64_t i0, uint64_t i1, const void *actions,
                    uint32_t act_stride, void *masks2, void *pmasks, uint32_t *srng, uint8_t *actions_out) {
+  if (use_pdl())
+    COG_LAUNCH_PDL(cog::k_step_single<SAMPLED>, blocks_for(i1 - i0), cog::BLOCK_THREADS, scratch_bytes(), stream, h->B,
+                   h->prm, i0, i1, (const uint8_t *)actions, act_stride, (uint8_t *)masks2, (uint8_t *)pmasks, srng,
+                   actions_out);
+  else
   COG_LAUNCH(cog::k_step_single<SAMPLED>, blocks_for(i1 - i0), cog::BLOCK_THREADS, scratch_bytes(), stream, h->B, h->prm,
              i0, i1, (const uint8_t *)actions, act_stride, (uint8_t *)masks2, (uint8_t *)pmasks, srng, actions_out);
 }
@@ -386,9 +422,9 @@ int cog_vec_step(cog_vec *h, const void *d_actions) {
   if (!h || !d_actions) return fail(COG_ERR_INVALID, "NULL argument");
   if (!h->seeded) return fail(COG_ERR_NOT_RESET, "step() before reset()");
   CK(cudaSetDevice(h->device));
-  time_begin(h);
+  if (step_events()) time_begin(h);
   launch_single<false>(h, h->stream, 0, h->n, d_actions, COG_ACTION_SIZE, nullptr, nullptr, nullptr, nullptr);
-  time_end(h);
+  if (step_events()) time_end(h);
   h->host_steps += h->n;
   g_launches++;
   CK(cudaGetLastError());
@@ -408,9 +444,9 @@ int cog_vec_step_sampled(cog_vec *h, cog_sampler *s) {
   if (!h->seeded) return fail(COG_ERR_NOT_RESET, "step() before reset()");
   CK(cudaSetDevice(h->device));
   if (s->stream != h->stream) CK(cudaStreamSynchronize(s->stream));
-  time_begin(h);
+  if (step_events()) time_begin(h);
   launch_single<true>(h, h->stream, 0, h->n, nullptr, COG_ACTION_SIZE, nullptr, nullptr, s->srng, s->actions);
-  time_end(h);
+  if (step_events()) time_end(h);
   h->host_steps += h->n;
   g_launches++;
   CK(cudaGetLastError());
@@ -739,10 +775,10 @@ int cog_vec_step_packed_host_io(cog_vec *h, const void *h_pactions, void *h_pmas
   if (!h->pk_actions) CK(cudaMalloc(&h->pk_actions, h->n * COGL_PACKED_ACTION_SIZE));
   if (!h->pk_masks) CK(cudaMalloc(&h->pk_masks, h->n * COGL_PACKED_MASK_SIZE));
   CK(cudaMemcpyAsync(h->pk_actions, h_pactions, h->n * COGL_PACKED_ACTION_SIZE, cudaMemcpyHostToDevice, h->stream));
-  time_begin(h);
+  if (step_events()) time_begin(h);
   launch_single<false>(h, h->stream, 0, h->n, h->pk_actions, COGL_PACKED_ACTION_SIZE, nullptr,
                        h_pmasks_out ? h->pk_masks : nullptr, nullptr, nullptr);
-  time_end(h);
+  if (step_events()) time_end(h);
   h->host_steps += h->n;
   g_launches++;
   CK(cudaGetLastError());

@@ -318,9 +318,11 @@ COG_API int cog_vec_stats_reset(cog_vec *h);
 COG_API int cog_sync(cog_vec *h);
 /* number of kernels this library has launched on behalf of this process */
 COG_API uint64_t cog_kernel_launches(void);
-/* elapsed device time (ms) of the most recent cog_vec_step / cog_vec_run_fused /
- * cog_sampler_sample kernel on this handle, measured with CUDA events on the
- * handle's stream; synchronises */
+/* elapsed device time (ms) of the most recent cog_vec_run_fused / cog_vec_run_fused_ex launch (both kernels)
+ * on this handle, measured with CUDA events on the handle's stream; synchronises.  Single steps
+ * (cog_vec_step, cog_vec_step_sampled) are timed only when the process runs with COG_STEP_EVENTS=1: a timing
+ * event between two kernels of a stream is a serialisation point that costs the per-step loop 12 %, and the
+ * per-step kernels use programmatic dependent launch (COG_PDL=0 turns that off). */
 COG_API int cog_vec_last_kernel_ms(cog_vec *h, float *ms);
 
 #ifdef __cplusplus

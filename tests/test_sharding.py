@@ -79,3 +79,19 @@ def test_two_ranks_equal_one_process(tmp_path, oracle_cls):
         for k, v in ref.items():  # every exported buffer of the shard == that slice of the single run
             assert z[k].tobytes() == v[lo:hi].tobytes(), (rank, k)
     one.close(); o.close()
+
+
+def test_numa_lookup_of_a_pci_device(tmp_path):
+    """shard.numa_cpus_of_pci reads the node and its CPU list from sysfs; unknown devices and single-node
+    platforms (numa_node = -1) give None"""
+    from gym_eldorado_b200 import shard
+    dev = tmp_path / "bus/pci/devices/0000:1b:00.0"
+    dev.mkdir(parents=True)
+    (dev / "numa_node").write_text("1\n")
+    node = tmp_path / "devices/system/node/node1"
+    node.mkdir(parents=True)
+    (node / "cpulist").write_text("16-31,48-50\n")
+    assert shard.numa_cpus_of_pci("0000:1B:00.0", str(tmp_path)) == (1, set(range(16, 32)) | {48, 49, 50})
+    (dev / "numa_node").write_text("-1\n")
+    assert shard.numa_cpus_of_pci("0000:1b:00.0", str(tmp_path)) is None
+    assert shard.numa_cpus_of_pci("0000:ff:00.0", str(tmp_path)) is None

@@ -27,7 +27,10 @@ for mode in modes:
     for _ in range(it): go()
     e1.record(); torch.cuda.synchronize()
     us = e0.elapsed_time(e1) * 1e3 / it
-    print("%-24s %-28s %8.1f us per sample+step  %.3e env-steps/s  (last kernel %.1f us)" % (
-        name, "k_sample + k_step_single" if mode == "two" else "cog_vec_step_sampled", us, n / us * 1e6,
-        v.last_kernel_ms() * 1e3))
+    try:
+        last = "%.1f us" % (v.last_kernel_ms() * 1e3)
+    except capi.CogError:
+        last = "not timed"
+    print("%-24s %-28s %8.1f us per sample+step  %.3e env-steps/s  (last kernel %s)" % (
+        name, "k_sample + k_step_single" if mode == "two" else "cog_vec_step_sampled", us, n / us * 1e6, last))
     v.close(); s.close()
