@@ -78,7 +78,7 @@ class ClockSampler(threading.Thread):
     """SM clock and throttle reasons DURING the timed region (profiling recipe's clocks line).  Read through
     NVML inside this process (one nvmlInit before the timed region, then two cheap queries every 20 ms): a
     fresh `nvidia-smi` process per sample attaches to the driver each time and stalls the GPU for 8-15 ms —
-    measured here as 5.23e9 env-steps/s without sampling against 4.5-5.2e9 with it (gpurun_out/r02_o.txt).
+    measured here as 5.23e9 env-steps/s without sampling against 4.5-5.2e9 with it (profiles/r02_o_clock_sampling.txt).
     Falls back to nvidia-smi (one sample every 0.5 s) when NVML cannot be loaded."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")

@@ -161,7 +161,7 @@ void time_end(cog_vec *h) {
 }
 /* Single steps are NOT bracketed by timing events unless COG_STEP_EVENTS=1: a timing event between two
  * kernels of a stream is a full serialisation point (measured: 44.0 us per sample+step of 65 536 envs with
- * the events, 38.9 us without, 36.5 us with programmatic dependent launch on top — gpurun_out/r02_l). */
+ * the events, 38.9 us without, 36.5 us with programmatic dependent launch on top — profiles/r02_l_api_loop_events_pdl.txt). */
 bool step_events() {
   static const bool on = std::getenv("COG_STEP_EVENTS") && std::atoi(std::getenv("COG_STEP_EVENTS")) != 0;
   return on;
