@@ -101,6 +101,14 @@ def merged_masks(snap):
     return m
 
 
+def player_masks(snap):
+    """Regime P: the current agent's own ActionMask record, as the reference's C++ doctests
+    use it — legal-looking plays the shared mask would have refused (u8 pile counters wrap)."""
+    n = len(snap["observations"])
+    agent = np.asarray(snap["agent_selection"]).astype(np.int64)
+    return snap["observations"]["player_data"][np.arange(n), agent]["action_mask"].copy()
+
+
 def first_mismatch(a, b):
     for name in ("observations", "selected_action_masks", "infos", "actions"):
         x, y = pb(a[name]), pb(b[name])
@@ -136,7 +144,7 @@ def run_parity(library, oracle_cls, n, seed, difficulty, max_steps, steps, regim
             else:
                 if check_every != 1:
                     snap = c.snapshot()
-                m = merged_masks(snap)
+                m = player_masks(snap) if regime == "P" else merged_masks(snap)
                 o.sample(m)
                 c.sample(m)
             o.step()

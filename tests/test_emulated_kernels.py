@@ -16,6 +16,10 @@ from gym_eldorado_b200 import capi, layout
     (8, 99, layout.HARD, 8, 300, "A", 3),
     (16, 5, layout.HARD, 8, 500, "S", 4),       # sample + step in one kernel (cog_vec_step_sampled)
     (8, 6, layout.EASY, 100000, 300, "S", 2),
+    (16, 5, layout.EASY, 100000, 400, "P", 4),  # regime P: the agent's own mask record (plays S would refuse)
+    (16, 9, layout.HARD, 20, 400, "P", 4),
+    (16, 3, layout.MEDIUM, 0, 40, "M", 4),      # max_steps = 0: every step ends an episode
+    (16, 3, layout.MEDIUM, 1, 60, "A", 4),
 ])
 def test_emulated_trajectory_parity(emu, oracle_cls, n, seed, difficulty, max_steps, steps, regime, n_players):
     parity.run_parity(emu, oracle_cls, n, seed, difficulty, max_steps, steps, regime, n_players=n_players)
@@ -48,6 +52,12 @@ def test_emulated_map_failure(emu):
 
 def test_emulated_offset_shard(emu, oracle_cls):
     parity.run_parity(emu, oracle_cls, 8, 31337, layout.MEDIUM, 50, 150, "M", offset=1000)
+
+
+@pytest.mark.parametrize("max_steps", [0, 1])
+def test_emulated_fused_every_step_ends_an_episode(emu, oracle_cls, max_steps):
+    st = parity.run_fused_merged_parity(emu, oracle_cls, 16, 11, layout.MEDIUM, max_steps, (1, 3, 7))
+    assert st["env_steps"] == 16 * 11 and st["episodes"] == st["truncations"] > 0
 
 
 def test_emulated_fused_merged_masks(emu, oracle_cls):

@@ -32,6 +32,11 @@ def oracle_cls(gpu_oracle_cls):
     (256, 12345, layout.EASY, 100000, 2000, "S", 4),   # configs[1] through the one-kernel sample + step
     (1024, 4242, layout.HARD, 8, 500, "S", 4),
     (64, 31, layout.MEDIUM, 12, 500, "S", 3),
+    (256, 5, layout.EASY, 100000, 3000, "P", 4),       # regime P: the agent's own mask record
+    (256, 9, layout.HARD, 20, 2000, "P", 4),
+    (256, 3, layout.MEDIUM, 0, 100, "M", 4),           # max_steps = 0: every step ends an episode (App. A#8)
+    (256, 3, layout.MEDIUM, 0, 100, "S", 4),
+    (256, 3, layout.MEDIUM, 1, 300, "M", 4),
 ])
 def test_trajectory_parity(cuda_lib, oracle_cls, n, seed, difficulty, max_steps, steps, regime, n_players):
     parity.run_parity(cuda_lib, oracle_cls, n, seed, difficulty, max_steps, steps, regime,
@@ -151,6 +156,17 @@ def test_fused_merged_masks(cuda_lib, oracle_cls, n, difficulty, max_steps, n_pl
                                         n_players=n_players)
     assert st["episodes"] > 0 and st["travelled_hexes"] > 0
     assert st["env_steps"] == n * 361
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("max_steps", [0, 1, 2])
+def test_fused_every_step_ends_an_episode(cuda_lib, oracle_cls, max_steps):
+    """max_steps = 0 / 1 / 2: the hot kernel parks (almost) every env at once and the tail
+    kernel does the episode ends, board generation and the remaining iterations"""
+    st = parity.run_fused_merged_parity(cuda_lib, oracle_cls, 1024, 11, layout.MEDIUM, max_steps, (1, 3, 20))
+    assert st["env_steps"] == 1024 * 24 and st["episodes"] == st["truncations"] > 0
+    if max_steps == 0:
+        assert st["episodes"] == st["env_steps"]
 
 
 @pytest.mark.gpu
