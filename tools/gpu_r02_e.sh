@@ -8,8 +8,8 @@ T=${1:-r02_e}
 tail -14 gpurun_out/${T}_gpu_tests.txt
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${T}_smoke.txt 2>&1; echo "smoke exit $?" >> gpurun_out/${T}_smoke.txt
 tail -2 gpurun_out/${T}_smoke.txt
-( time timeout 900 python bench.py --steps 10 --warmup 3 ) > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo "bench exit $?"; tail -4 gpurun_out/${T}_bench.err
-timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/${T}_bench_reference.json 2> gpurun_out/${T}_ref.err; echo "ref exit $?"
+( time timeout 900 python bench.py --steps 20 --warmup 5 ) > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo "bench exit $?"; tail -4 gpurun_out/${T}_bench.err
+timeout 600 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/${T}_bench_reference.json 2> gpurun_out/${T}_ref.err; echo "ref exit $?"
 if [ "${2:-ncu}" = "ncu" ]; then
   SMALL="timeout 300 python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline --no-resets --no-side"
   $SMALL > gpurun_out/${T}_plain.log 2>&1 &&
