@@ -1684,46 +1684,5 @@ __device__ __forceinline__ bool sample_action(u32 &rng, u32 play, u32 spec, u32 
   return false;
 }
 
-/* ---- sample_action for a loop that calls it back to back (the fused kernel) ------------------------------
- * The four unit draws that end a sample() of the reference's own flow are not applied at once but merged
- * into the NEXT call's first draw: output = state a^4 a = state a^5 — ONE modular multiply per step instead
- * of two.  `pend` (0 / 1): the state still owes those four draws; flush_unit_draws() settles the debt
- * before the state is stored or handed to any other consumer. */
-__device__ __forceinline__ u32 minstd_mul(u32 s, u32 m) { /* s m mod (2^31 - 1), both < 2^31 */
-  const u64 t = (u64)s * m;                           /* < 2^62 */
-  const u64 f = (t & 0x7fffffffull) + (t >> 31);      /* < 2^32 */
-  u32 r = (u32)(f & 0x7fffffffull) + (u32)(f >> 31);
-  if (r >= 0x7fffffffu) r -= 0x7fffffffu;
-  return r;
-}
-__device__ __forceinline__ void flush_unit_draws(u32 &rng, u32 &pend) {
-  if (pend) {
-    if (COG_UNLIKELY(!minstd_skip4_unit_draws(rng)))
-      for (int k = 0; k < 4; ++k) sample_head(rng, 1u);
-    pend = 0u;
-  }
-}
-__device__ __forceinline__ bool sample_action_deferred(u32 &rng, u32 &pend, u32 play, u32 spec, u32 rem, u32 ms,
-                                                       u32 &act, u32 &a_shop, int lane) {
-  if (spec == 1u && rem == 1u && ms == 0x81u) {
-    /* the pending draws reject for exactly the four states minstd_skip4_unit_draws() names */
-    const bool guard = pend && (rng == 739806647u || rng == 671875339u || rng == 939811632u || rng == 1785685951u);
-    if (COG_LIKELY(!guard)) {
-      const ud_entry e = UD_TAB[__popc(play)];
-      const u32 x = minstd_mul(rng, pend ? 1144108930u : 16807u); /* a^5 (checked below MINSTD_POW_LANE) : a */
-      const u32 r = x - 1u;
-      if (COG_LIKELY(r < e.past)) {
-        rng = x;
-        pend = 1u;
-        a_shop = 0;
-        act = nth_set_bit_warp(play, ud_quotient(r, e), lane);
-        return true;
-      }
-    }
-  }
-  flush_unit_draws(rng, pend);
-  return sample_action(rng, play, spec, rem, ms, act, a_shop, lane);
-}
-
 }  // namespace cog
 #endif /* COG_DEVICE_CUH */

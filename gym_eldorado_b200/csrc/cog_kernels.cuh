@@ -291,18 +291,14 @@ __device__ __forceinline__ void store_action(u8 *actions_out, u64 i, u32 act, u3
  * the current agent ("regime M": moves, purchases, removals, wins — every branch of step). */
 /* ROLLOUT = true: a compact record of the state, the mask heads sampled from, the action and
  * the outcome goes to `rec` — two coalesced stores per env-step. */
-/* DEFER (the hot kernel's loop): the sampler's trailing unit draws are merged into the next call
- * (sample_action_deferred; `pend` = the state owes them) */
-template <bool MERGED, bool ROLLOUT, bool DEFER = false>
+template <bool MERGED, bool ROLLOUT>
 __device__ __forceinline__ u32 sample_and_step(Env &E, u32 &sr, u32 &act, u32 &a_shop, const Params &prm,
                                                const Buffers &B, u64 i, bool &obs_pending, u8 *rec, u32 t,
-                                               int lane, u32 *pend = nullptr) {
+                                               int lane) {
   u32 status;
   if (MERGED) {
     u32 rem, ms;
     merged_heads(E, lane, rem, ms);
-    if (DEFER) sample_action_deferred(sr, *pend, E.Splay, spec_of(E.Splay), rem, ms, act, a_shop, lane);
-    else
     sample_action(sr, E.Splay, spec_of(E.Splay), rem, ms, act, a_shop, lane);
     if (ROLLOUT) compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), rem, ms, act, a_shop, t, lane);
     /* most steps are still card plays and nulls: they take the instantiation whose other branches fold away */
@@ -312,8 +308,7 @@ __device__ __forceinline__ u32 sample_and_step(Env &E, u32 &sr, u32 &act, u32 &a
 #endif
       status = env_step<false, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
   } else {
-    const bool play_only = DEFER ? sample_action_deferred(sr, *pend, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane)
-                                 : sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane);
+    const bool play_only = sample_action(sr, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, lane);
     if (ROLLOUT) compact_store_pre(rec, E, prm, E.Splay, spec_of(E.Splay), E.Srem, E.Sms, act, a_shop, t, lane);
     if (play_only) status = env_step<true, true>(E, act, 0, prm, B, i, obs_pending, lane);
     else status = env_step<true, false>(E, act, a_shop, prm, B, i, obs_pending, lane);
@@ -372,26 +367,15 @@ __global__ void __launch_bounds__(BLOCK_THREADS, ROLLOUT ? (MERGED ? COG_RING_BL
     bool obs_pending = false;
     u32 k = k_steps;
     u32 slot = R.slot0, t = R.t0;
-#ifdef COG_DEFER_UNIT_DRAWS
-    u32 pend = 0;
-#endif
     do {
-#ifdef COG_DEFER_UNIT_DRAWS
-      status = sample_and_step<MERGED, ROLLOUT, true>(E, sr, act, a_shop, prm, B, i, obs_pending,
-                                                      ROLLOUT ? rollout_rec(R, (u32)i, slot) : nullptr, t, lane, &pend);
-#else
       status = sample_and_step<MERGED, ROLLOUT>(E, sr, act, a_shop, prm, B, i, obs_pending,
                                                 ROLLOUT ? rollout_rec(R, (u32)i, slot) : nullptr, t, lane);
-#endif
       if (ROLLOUT) {
         ++t;
         if (++slot == R.T) slot = 0;
       }
       --k;
     } while (k && !(status & 1u));
-#ifdef COG_DEFER_UNIT_DRAWS
-    flush_unit_draws(sr, pend);
-#endif
     steps_done += k_steps - k;
     const u32 parked = (status & 1u) ? k + 1u : 0u;
     if (obs_pending) env_update_observation(E, (int)E.agent, 0, E.cpc, lane);
