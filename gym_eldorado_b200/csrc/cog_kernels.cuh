@@ -66,6 +66,17 @@ __global__ void k_init(Buffers B, u64 n) {
   export_dynamic(E, B, i, 0xffu, lane);
 }
 
+/* re-broadcast of the env scalars from lane 0: the same values, but provably warp-uniform for ptxas */
+__device__ __forceinline__ void env_prove_uniform(Env &E) {
+  E.rng = bcast(E.rng, 0); E.turn = bcast(E.turn, 0); E.agent = bcast(E.agent, 0);
+  E.phase = bcast(E.phase, 0); E.n_in_market = bcast(E.n_in_market, 0);
+  E.cpf = bcast(E.cpf, 0); E.cpc = bcast(E.cpc, 0); E.info_steps = bcast(E.info_steps, 0);
+  E.Splay = bcast(E.Splay, 0); E.Srem = bcast(E.Srem, 0); E.Sms = bcast(E.Sms, 0);
+  E.res[0] = (int)bcast((u32)E.res[0], 0); E.res[1] = (int)bcast((u32)E.res[1], 0);
+  E.res[2] = (int)bcast((u32)E.res[2], 0);
+  E.minx = (int)bcast((u32)E.minx, 0); E.miny = (int)bcast((u32)E.miny, 0);
+}
+
 /* vec_cog_env<N>::reset include/vec_environment.h:33-44.  reseed: env i restarts its RNG
  * from uint32(seed_base + i) (cog_env::reset(seed, ...) src/environment.cpp:66-77). */
 #ifndef COG_RESET_BLOCKS
@@ -73,10 +84,20 @@ __global__ void k_init(Buffers B, u64 n) {
 #endif
 __global__ void __launch_bounds__(BLOCK_THREADS, COG_RESET_BLOCKS) k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed) {
   const int lane = threadIdx.x & 31;
+#ifndef COG_NO_UNIFORM_PROOF
+  /* warp index and env scalars through shuffles from a fixed lane: board generation is all warp-uniform
+   * control flow, and ptxas only compiles it that way when it can prove it (see k_step_fused): 4 016 -> 2 800
+   * instructions, BSSY 112 -> 26, BRA.DIV 41 -> 0; 1.21 -> 1.29e8 resets/s */
+  const u64 i = env_index(blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0));
+#else
   const u64 i = env_index(blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5));
+#endif
   if (i >= n) return;
   Env E;
   env_load(E, B.hidden + i * COG_HID_WORDS, lane);
+#ifndef COG_NO_UNIFORM_PROOF
+  env_prove_uniform(E);
+#endif
   if (reseed) E.rng = minstd_seed((u64)(u32)(seed_base + i));
   const int rc = env_reset(E, prm, B, i, warp_scratch(), lane);
   env_store(E, B.hidden + i * COG_HID_WORDS, lane, 0, rc ? 1u : 0u); /* a failed env ignores steps until a reset succeeds */
@@ -272,7 +293,9 @@ __device__ __forceinline__ void store_action(u8 *actions_out, u64 i, u32 act, u3
  * parked.  The hot kernel is small (about 3 000 instructions against 9 000 with board
  * generation inlined) and its register allocation is not shaped by the cold paths. */
 #ifndef COG_TAIL_BLOCKS
-#define COG_TAIL_BLOCKS 8 /* board generation is latency-bound: occupancy beats spills */
+#define COG_TAIL_BLOCKS 10 /* board generation is latency-bound: occupancy beats spills (reset-heavy configs[3] shape, with
+                            * the uniform proof: 6 blocks 2.33e9, 7 2.32e9, 8 2.41e9, 9 2.46e9, 10 2.46e9 env-steps/s;
+                            * regime M with episode ends 2.13 / 2.17 / 2.16 / 2.19 / 2.28e9) */
 #endif
 /* resident blocks per SM of the fused kernels that also write the rollout ring: the record
  * assembly wants registers more than a ninth block (measured: 7 blocks 3.31e9, 8 3.17e9, 9 2.97e9
@@ -353,13 +376,7 @@ __global__ void __launch_bounds__(BLOCK_THREADS, ROLLOUT ? (MERGED ? COG_RING_BL
     u32 sr = srng[i];
 #ifndef COG_NO_UNIFORM_PROOF
     /* the same values, provably warp-uniform again (loads are not, shuffles from lane 0 are) */
-    E.rng = bcast(E.rng, 0); E.turn = bcast(E.turn, 0); E.agent = bcast(E.agent, 0);
-    E.phase = bcast(E.phase, 0); E.n_in_market = bcast(E.n_in_market, 0);
-    E.cpf = bcast(E.cpf, 0); E.cpc = bcast(E.cpc, 0); E.info_steps = bcast(E.info_steps, 0);
-    E.Splay = bcast(E.Splay, 0); E.Srem = bcast(E.Srem, 0); E.Sms = bcast(E.Sms, 0);
-    E.res[0] = (int)bcast((u32)E.res[0], 0); E.res[1] = (int)bcast((u32)E.res[1], 0);
-    E.res[2] = (int)bcast((u32)E.res[2], 0);
-    E.minx = (int)bcast((u32)E.minx, 0); E.miny = (int)bcast((u32)E.miny, 0);
+    env_prove_uniform(E);
     sr = bcast(sr, 0);
 #endif
     if (COG_UNLIKELY(E.dead)) continue; /* failed board generation: ignored until reset() */
@@ -403,19 +420,34 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Bu
                                                                              u8 *actions_out, u32 k_steps, Rollout R) {
   const int lane = threadIdx.x & 31;
   if (*(volatile unsigned *)&B.park[0] == *(volatile unsigned *)&B.park[1]) return; /* nothing parked */
+  /* the uniform proof of k_step_fused, here as well — after the load AND after every reset (the scalars
+   * board generation leaves behind are not provably uniform either): BSSY 322 -> 51, BRA.DIV 103 -> 0;
+   * reset-heavy configs[3] 1.91 -> 2.42e9 env-steps/s, regime M with episode ends 1.66 -> 2.17e9 */
+#ifndef COG_NO_UNIFORM_PROOF
+  const u32 warp0 = blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0);
+#else
   const u32 warp0 = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+#endif
   const u32 stride = gridDim.x * WARPS_PER_BLOCK;
   BoardScratch &sc = warp_scratch();
   u64 steps_done = 0;
   u32 n_handled = 0;
   for (u32 i32 = warp0; i32 < (u32)n; i32 += stride) {
     const u64 i = env_index(i32);
+#ifndef COG_NO_UNIFORM_PROOF
+    const u32 parked = bcast(B.hidden[i * COG_HID_WORDS + COG_HL_ENV * 32 + COG_ES_PENDING], 0);
+#else
     const u32 parked = B.hidden[i * COG_HID_WORDS + COG_HL_ENV * 32 + COG_ES_PENDING];
+#endif
     if (!parked) continue;
     ++n_handled;
     Env E;
     env_load(E, B.hidden + i * COG_HID_WORDS, lane);
     u32 sr = srng[i];
+#ifndef COG_NO_UNIFORM_PROOF
+    env_prove_uniform(E);
+    sr = bcast(sr, 0);
+#endif
     u32 act = 0, a_shop = 0, status = 1;
     bool obs_pending = false;
     const u32 k = parked - 1u;
@@ -437,6 +469,9 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Bu
           dead = 1; /* reported at the next synchronising call; the env ignores steps until reset() */
           break;
         }
+#ifndef COG_NO_UNIFORM_PROOF
+        env_prove_uniform(E);
+#endif
       }
       if (j == k) break;
       if (ROLLOUT) {
