@@ -261,8 +261,9 @@ void launch_single(cog_vec *h, cudaStream_t stream, uint64_t i0, uint64_t i1, co
                    h->prm, i0, i1, (const uint8_t *)actions, act_stride, (uint8_t *)masks2, (uint8_t *)pmasks, srng,
                    actions_out);
   else
-  COG_LAUNCH(cog::k_step_single<SAMPLED>, blocks_for(i1 - i0), cog::BLOCK_THREADS, scratch_bytes(), stream, h->B, h->prm,
-             i0, i1, (const uint8_t *)actions, act_stride, (uint8_t *)masks2, (uint8_t *)pmasks, srng, actions_out);
+    COG_LAUNCH(cog::k_step_single<SAMPLED>, blocks_for(i1 - i0), cog::BLOCK_THREADS, scratch_bytes(), stream, h->B,
+               h->prm, i0, i1, (const uint8_t *)actions, act_stride, (uint8_t *)masks2, (uint8_t *)pmasks, srng,
+               actions_out);
 }
 
 template <bool MERGED, bool ROLLOUT>

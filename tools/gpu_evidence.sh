@@ -1,9 +1,9 @@
 #!/bin/bash
-# gpurun call E: the whole -m gpu suite, smoke, the new bench line (+ reference arm), launch list and full ncu
+# gpurun evidence call (gpurun -- "bash tools/gpu_evidence.sh TAG ncu"): the whole -m gpu suite, smoke, the new bench line (+ reference arm), launch list and full ncu
 # captures of the four kernels the bench line talks about.
 set -u
 mkdir -p gpurun_out
-T=${1:-r02_e}
+T=${1:-run}
 ( time timeout 1800 python -m pytest tests -m gpu -q -x --durations=8 ) > gpurun_out/${T}_gpu_tests.txt 2>&1; echo "pytest exit $?" >> gpurun_out/${T}_gpu_tests.txt
 tail -14 gpurun_out/${T}_gpu_tests.txt
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${T}_smoke.txt 2>&1; echo "smoke exit $?" >> gpurun_out/${T}_smoke.txt
