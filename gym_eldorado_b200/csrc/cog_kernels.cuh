@@ -80,7 +80,8 @@ __device__ __forceinline__ void env_prove_uniform(Env &E) {
 /* vec_cog_env<N>::reset include/vec_environment.h:33-44.  reseed: env i restarts its RNG
  * from uint32(seed_base + i) (cog_env::reset(seed, ...) src/environment.cpp:66-77). */
 #ifndef COG_RESET_BLOCKS
-#define COG_RESET_BLOCKS 7
+#define COG_RESET_BLOCKS 12 /* with provably uniform control flow, occupancy beats spills: 7 blocks (72 registers) 1.39e8,
+                             * 9 1.44e8, 12 (40 registers) 1.50e8, 14 / 16 (32) 1.49e8 resets/s (profiles/r02_y_resident_blocks.txt) */
 #endif
 __global__ void __launch_bounds__(BLOCK_THREADS, COG_RESET_BLOCKS) k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed) {
   const int lane = threadIdx.x & 31;
@@ -293,9 +294,10 @@ __device__ __forceinline__ void store_action(u8 *actions_out, u64 i, u32 act, u3
  * parked.  The hot kernel is small (about 3 000 instructions against 9 000 with board
  * generation inlined) and its register allocation is not shaped by the cold paths. */
 #ifndef COG_TAIL_BLOCKS
-#define COG_TAIL_BLOCKS 10 /* board generation is latency-bound: occupancy beats spills (reset-heavy configs[3] shape, with
-                            * the uniform proof: 6 blocks 2.33e9, 7 2.32e9, 8 2.41e9, 9 2.46e9, 10 2.46e9 env-steps/s;
-                            * regime M with episode ends 2.13 / 2.17 / 2.16 / 2.19 / 2.28e9) */
+#define COG_TAIL_BLOCKS 16 /* board generation is latency-bound: occupancy beats spills.  Reset-heavy configs[3] shape, with
+                            * the uniform proof: 6 blocks 2.33e9, 8 2.41e9, 10 2.46e9 env-steps/s; with dirty-chunk clearing
+                            * 10 / 12 / 16 blocks 2.60 / 2.54 / 2.60e9; regime M with episode ends (EASY, max_steps 40)
+                            * 2.38 / 2.45 / 2.59e9 (profiles/r02_y_resident_blocks.txt) */
 #endif
 /* resident blocks per SM of the fused kernels that also write the rollout ring: the record
  * assembly wants registers more than a ninth block (measured: 7 blocks 3.31e9, 8 3.17e9, 9 2.97e9
@@ -307,7 +309,7 @@ __device__ __forceinline__ void store_action(u8 *actions_out, u64 i, u32 act, u3
 #define COG_RING_BLOCKS_MERGED 8
 #endif
 #ifndef COG_MIN_BLOCKS
-#define COG_MIN_BLOCKS 9
+#define COG_MIN_BLOCKS 16 /* full occupancy at 32 registers, no spills: 9 blocks (52 registers) 5.25e9, 12 (40) 5.58e9, 13-16 (32) 5.60e9 env-steps/s; regime M 3.19 / 3.41 / 3.53e9 (profiles/r02_y_resident_blocks.txt) */
 #endif
 /* MERGED = false: actions sampled from selected_action_masks (the reference's own flow,
  * "regime A": only `play` ever has a choice).  MERGED = true: from the merged legal mask of
