@@ -1,0 +1,255 @@
+"""Time-boxed randomised parity campaign on the CPU: the kernels under the lock-step warp emulator
+(tests/emu) against the C restatement (oracle/cog_oracle.c) on random configurations — env counts
+with ragged last warps, env-index offsets, 2..4 players, 1..8 pieces, all difficulties, max_steps
+from 0 to "never", and every way of driving the path (single steps in regimes A / M / P / S, the
+fused kernel with selected and with merged masks in random chunk sizes, a mid-episode reset()).
+
+Test infrastructure (the oracle is the checker); prints one line per failing case with the
+arguments that reproduce it and exits 1 if any case failed.
+
+    python tools/fuzz_emulated.py --seconds 600 --seed 1 [--jobs 8]
+    python tools/fuzz_emulated.py --pair port-ref ...   # the restatement against the compiled reference
+    python tools/fuzz_emulated.py --pair cuda-port ...  # on a GPU box: the product library itself
+"""
+import argparse
+import multiprocessing as mp
+import os
+import random
+import sys
+import time
+import traceback
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def draw_case(rng):
+    mode = rng.choice(["A", "M", "M", "P", "S", "fusedA", "fusedM", "fusedM", "midreset",
+                       "hostio", "packedio", "rollout"])
+    n_players = rng.choice([4, 4, 4, 3, 2])
+    case = {
+        "mode": mode,
+        "n": rng.choice([1, 2, 3, 5, 8, 9, 16, 31, 32, 33, 40]),
+        "seed": rng.randrange(0, 2 ** 31 - 1),
+        "offset": rng.choice([0, 0, 0, rng.randrange(1, 1 << 20)]),
+        "n_players": n_players,
+        "n_pieces": rng.choice([1, 2, 3, 3, 3, 4, 5, 6, 7, 8]),
+        "difficulty": rng.randrange(3),
+        "max_steps": rng.choice([0, 1, 2, 5, 8, 13, 30, 60, 200, 100000, 100000]),
+        "steps": rng.choice([60, 150, 400]),
+        "chunks": [rng.choice([0, 1, 2, 7, 33, 100]) for _ in range(rng.randrange(1, 5))],
+        "n_slots": rng.choice([1, 2, 16, 64, 1024]),
+        "io_regime": rng.choice(["A", "M"]),
+    }
+    return case
+
+
+def run_case(case, emu, oracle_cls):
+    import parity
+    from gym_eldorado_b200 import capi
+    from oracle import port
+    n, seed, off = case["n"], case["seed"], case["offset"]
+    args = (seed, case["n_players"], case["n_pieces"], case["difficulty"], case["max_steps"])
+    # a board the reference cannot generate must fail on both sides, and the same way
+    probe = oracle_cls(n, seed, off)
+    try:
+        probe.reset(*args)
+        board_ok = True
+    except port.MapGenerationError:
+        board_ok = False
+    finally:
+        probe.close()
+    if not board_ok:
+        c = parity.Candidate(emu, n, seed, off)
+        try:
+            c.reset(*args)
+        except capi.MapGenerationError:
+            return "map_failure"
+        finally:
+            c.close()
+        raise AssertionError("the oracle fails to generate a board, the kernels did not")
+    mode = case["mode"]
+    if mode in ("A", "M", "P", "S"):
+        try:
+            parity.run_parity(emu, oracle_cls, n, seed, case["difficulty"], case["max_steps"], case["steps"], mode,
+                              n_players=case["n_players"], n_pieces=case["n_pieces"], offset=off)
+        except (port.MapGenerationError, capi.MapGenerationError):
+            return _auto_reset_failure(case, emu, oracle_cls)
+        return mode
+    if mode == "midreset":
+        if off:
+            return "skipped"
+        # the helper asserts that the reset interrupts games with cards in play: enough envs, and
+        # episodes long enough to have a turn under way
+        try:
+            parity.run_mid_episode_reset(lambda k, s: parity.Candidate(emu, k, s), oracle_cls, max(n, 8), seed,
+                                         case["difficulty"], max(case["max_steps"], 60), before=40, after=60)
+        except (port.MapGenerationError, capi.MapGenerationError):
+            return "map_failure_later"
+        return mode
+    if mode in ("hostio", "packedio", "rollout"):
+        # the helpers reset with 3 pieces (and 4 players for the I/O pair) at offset 0
+        try:
+            if mode == "rollout":
+                parity.run_rollout_parity(emu, oracle_cls, n, seed, case["difficulty"], case["max_steps"],
+                                          case["chunks"], case["n_slots"], case["io_regime"] == "M",
+                                          n_players=case["n_players"])
+            else:
+                run = parity.run_host_io_parity if mode == "hostio" else parity.run_packed_io_parity
+                run(emu, oracle_cls, n, seed, case["difficulty"], case["max_steps"], min(case["steps"], 150),
+                    case["io_regime"])
+        except (port.MapGenerationError, capi.MapGenerationError):
+            return "map_failure_later"
+        return mode
+    merged = mode == "fusedM"
+    o = oracle_cls(n, seed, off)
+    c = parity.Candidate(emu, n, seed, off)
+    try:
+        o.reset(*args)
+        c.reset(*args)
+        for k in case["chunks"]:
+            try:
+                for _ in range(k):
+                    if merged:
+                        o.sample(parity.merged_masks(parity.oracle_snapshot(o)))
+                    else:
+                        o.sample()
+                    o.step()
+            except port.MapGenerationError:
+                return "map_failure_later"
+            c.vec.run_fused(c.smp, k, merged=merged)
+            bad = parity.first_mismatch(c.snapshot(), parity.oracle_snapshot(o))
+            assert bad is None, bad
+        st = c.vec.stats()
+        assert st["env_steps"] == n * sum(case["chunks"]), st
+        assert st["resets"] == n + st["episodes"], st
+    finally:
+        c.close()
+        o.close()
+    return mode
+
+
+def run_case_port_vs_reference(case):
+    """the C restatement against the compiled UNMODIFIED reference (oracle/_ref) where the reference is
+    defined: 4 players, boards of at most 5 pieces, N among the shim's instantiations, offset 0"""
+    import parity
+    from oracle import port, refshim
+    n = min((k for k in (1, 16, 64) if k >= min(case["n"], 64)))
+    seed = case["seed"]
+    args = (seed, 4, min(case["n_pieces"], 5), case["difficulty"], case["max_steps"])
+    regime = {"A": "A", "S": "A", "fusedA": "A", "P": "P"}.get(case["mode"], "M")
+    o, r = port.OracleVec(n, seed), refshim.RefVec(n, seed)
+    try:
+        failed = [False, False]
+        for k, side in enumerate((o, r)):
+            try:
+                side.reset(*args)
+            except (port.MapGenerationError, RuntimeError):
+                failed[k] = True
+        assert failed[0] == failed[1], "board generation: port failed=%s reference failed=%s" % tuple(failed)
+        if failed[0]:
+            return "ref_map_failure"
+        bad = parity.first_mismatch(parity.oracle_snapshot(o), parity.oracle_snapshot(r))
+        assert bad is None, "after reset: " + bad
+        for s in range(case["steps"]):
+            if regime == "A":
+                o.sample(); r.sample()
+            else:
+                snap = parity.oracle_snapshot(r)
+                m = parity.player_masks(snap) if regime == "P" else parity.merged_masks(snap)
+                o.sample(m); r.sample(m)
+            failed = [False, False]
+            for k, side in enumerate((o, r)):
+                try:
+                    side.step()
+                except (port.MapGenerationError, RuntimeError):
+                    failed[k] = True
+            assert failed[0] == failed[1], "auto-reset board generation: port failed=%s reference failed=%s" % tuple(failed)
+            if failed[0]:
+                return "ref_map_failure_later"
+            bad = parity.first_mismatch(parity.oracle_snapshot(o), parity.oracle_snapshot(r))
+            assert bad is None, "step %d: %s" % (s, bad)
+            if case["mode"] == "midreset" and s == case["steps"] // 2:
+                o.reset(); r.reset()
+                bad = parity.first_mismatch(parity.oracle_snapshot(o), parity.oracle_snapshot(r))
+                assert bad is None, "right after reset(): " + bad
+    finally:
+        o.close(); r.close()
+    return "ref_" + regime
+
+
+def _auto_reset_failure(case, emu, oracle_cls):
+    # board generation failed inside an auto-reset: the reference throws out of step(); the kernels
+    # mark the env dead and report at the next synchronising call — both surfaced an error
+    return "map_failure_later"
+
+
+def worker(wid, a, q):
+    import parity
+    from oracle import port
+    port.build()
+    if a.pair == "cuda-port":
+        from gym_eldorado_b200 import capi
+        emu = capi.lib()  # the product library on a GPU box (fails loudly without one)
+    elif a.pair == "emu-port":
+        emu = parity.emu_lib()
+    else:
+        emu = None
+    rng = random.Random(a.seed * 1000 + wid)
+    t_end = time.time() + a.seconds
+    done, fails, kinds = 0, 0, {}
+    while time.time() < t_end and (a.cases == 0 or done < a.cases):
+        case = draw_case(rng)
+        try:
+            if a.pair == "port-ref":
+                kind = run_case_port_vs_reference(case)
+            else:
+                kind = run_case(case, emu, port.OracleVec)
+            kinds[kind] = kinds.get(kind, 0) + 1
+        except Exception as e:  # noqa: BLE001 - every failure is reported with its reproducer
+            fails += 1
+            print("FAIL %r\n  %s: %s" % (case, type(e).__name__, str(e)[:400]), flush=True)
+            if a.verbose:
+                traceback.print_exc()
+        done += 1
+    q.put((wid, done, fails, kinds))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--seconds", type=float, default=120.0)
+    ap.add_argument("--cases", type=int, default=0, help="stop each worker after this many cases (0 = time only)")
+    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--jobs", type=int, default=max(1, (os.cpu_count() or 2) - 1))
+    ap.add_argument("--pair", choices=["emu-port", "port-ref", "cuda-port"], default="emu-port",
+                    help="emu-port: emulated kernels vs the C restatement; port-ref: the C restatement vs oracle/_ref; "
+                         "cuda-port: the product library on a GPU box vs the C restatement")
+    ap.add_argument("--verbose", action="store_true")
+    a = ap.parse_args()
+    # build once before forking so the workers do not race on make
+    import parity
+    from oracle import port
+    port.build()
+    if a.pair == "emu-port":
+        parity.emu_lib()
+    q = mp.Queue()
+    ps = [mp.Process(target=worker, args=(w, a, q)) for w in range(a.jobs)]
+    for p in ps:
+        p.start()
+    total, fails, kinds = 0, 0, {}
+    for _ in ps:
+        _, d, f, k = q.get()
+        total += d
+        fails += f
+        for name, cnt in k.items():
+            kinds[name] = kinds.get(name, 0) + cnt
+    for p in ps:
+        p.join()
+    print("fuzz: %d cases, %d failures, by kind %s" % (total, fails, dict(sorted(kinds.items()))))
+    sys.exit(1 if fails else 0)
+
+
+if __name__ == "__main__":
+    main()
