@@ -6,7 +6,7 @@
  * step (+ auto-reset), mask maintenance and the masked random sampler, operating
  * on buffers with the reference's exported record layouts.
  *
- * PARITY PINNED: tests/test_oracle_vs_reference.py checks this file against the
+ * PARITY PINNED: tests/test_oracle.py checks this file against the
  * reference itself compiled here (oracle/_ref/libcog_ref.so, unmodified sources)
  * and against golden fixtures under tests/golden/ minted from that build.
  *
