@@ -328,7 +328,7 @@ int cog_vec_create(uint64_t n_envs, uint64_t env_index_offset, int device, void 
       {(void **)&h->B.infos, n * COG_INFO_SIZE},
       {(void **)&h->B.agents, n},
       {(void **)&h->B.stats, COG_STAT_COUNT * sizeof(unsigned long long)},
-      {(void **)&h->B.park, 2 * sizeof(unsigned)},
+      {(void **)&h->B.park, 4 * sizeof(unsigned)},
   };
   for (auto &b : bufs) {
     cudaError_t e = cudaMalloc(b.p, b.bytes);

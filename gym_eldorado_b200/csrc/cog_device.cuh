@@ -357,7 +357,8 @@ struct Buffers {
   u8 *agents;    /* [n] */
   unsigned long long *stats; /* [COG_STAT_COUNT] */
   int *err;      /* [0] first error code, [1] env index */
-  unsigned *park; /* [0] envs ever parked by k_step_fused, [1] envs k_step_tail picked up again */
+  unsigned *park; /* [0] envs ever parked by k_step_fused, [1] envs k_step_tail picked up again,
+                   * [2] env tickets handed out by the running k_step_fused, [3] by the running k_step_tail */
 };
 
 /* ROTATED PLAYER ORDER.  The seven words that hold one byte per player (the five piles,

@@ -368,10 +368,32 @@ __global__ void __launch_bounds__(BLOCK_THREADS, ROLLOUT ? (MERGED ? COG_RING_BL
 #else
   const u32 warp0 = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
 #endif
-  const u32 stride = gridDim.x * WARPS_PER_BLOCK;
   u64 steps_done = 0;
   u32 n_parked = 0;
+#ifndef COG_STATIC_ENVS
+  /* ENVS BY TICKET.  The warp schedulers do not advance the resident warps evenly: with a static grid-stride
+   * split (7 envs per warp at 65 536 envs) the warps that are served first leave early and the launch ends
+   * with a long stretch of few active warps per SM (ncu: 65 % of the resident warps active on average).  Here
+   * one counter hands out the envs: a warp that finishes takes the next one.  Measured against the static
+   * split (profiles/r02_ab_ticketed_units.txt): regime A 5.60 -> 5.99e9 env-steps/s, regime M 3.57 -> 3.91e9,
+   * regime M with episode ends 2.75 -> 3.02e9, reset-heavy configs[3] 2.69 -> 2.86e9; results identical (which
+   * warp steps an env changes nothing).  Splitting each env's steps into several smaller units to shorten the
+   * end of the launch further was measured as well and lost (one record round trip per unit: 5.4-5.5e9).
+   * The ticket comes back through a shuffle from lane 0, and the NEXT ticket is drawn in the loop body rather
+   * than at the loop's head: this is the shape ptxas still proves warp-uniform (a draw at the head costs the
+   * proof: BSSY 33 -> 204, BRA.DIV 0 -> 56, spills).  k_step_tail, which always follows, rewinds the counter. */
+  (void)warp0;
+  if (blockIdx.x == 0 && threadIdx.x == 0) B.park[3] = 0; /* k_step_tail's tickets */
+  u32 next = 0;
+  if (lane == 0) next = atomicAdd(&B.park[2], 1u);
+  for (next = bcast(next, 0); next < (u32)n;) {
+    const u32 i32 = next;
+    if (lane == 0) next = atomicAdd(&B.park[2], 1u);
+    next = bcast(next, 0);
+#else
+  const u32 stride = gridDim.x * WARPS_PER_BLOCK;
   for (u32 i32 = warp0; i32 < (u32)n; i32 += stride) {
+#endif
     const u64 i = env_index(i32);
     Env E;
     env_load(E, B.hidden + i * COG_HID_WORDS, lane);
@@ -421,6 +443,9 @@ template <bool MERGED, bool ROLLOUT>
 __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Buffers B, Params prm, u64 n, u32 *srng,
                                                                              u8 *actions_out, u32 k_steps, Rollout R) {
   const int lane = threadIdx.x & 31;
+#ifndef COG_STATIC_ENVS
+  if (blockIdx.x == 0 && threadIdx.x == 0) B.park[2] = 0; /* k_step_fused's tickets: rewound for the next launch */
+#endif
   if (*(volatile unsigned *)&B.park[0] == *(volatile unsigned *)&B.park[1]) return; /* nothing parked */
   /* the uniform proof of k_step_fused, here as well — after the load AND after every reset (the scalars
    * board generation leaves behind are not provably uniform either): BSSY 322 -> 51, BRA.DIV 103 -> 0;
@@ -434,7 +459,19 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_TAIL_BLOCKS) k_step_tail(Bu
   BoardScratch &sc = warp_scratch();
   u64 steps_done = 0;
   u32 n_handled = 0;
+#ifndef COG_STATIC_ENVS
+  /* envs by ticket, as in k_step_fused: what a parked env still owes differs by orders of magnitude
+   * (a reset and a few steps, or most of the launch), a static split leaves warps idle */
+  (void)warp0; (void)stride;
+  u32 next = 0;
+  if (lane == 0) next = atomicAdd(&B.park[3], 1u);
+  for (next = bcast(next, 0); next < (u32)n;) {
+    const u32 i32 = next;
+    if (lane == 0) next = atomicAdd(&B.park[3], 1u); /* drawn in the body: see k_step_fused */
+    next = bcast(next, 0);
+#else
   for (u32 i32 = warp0; i32 < (u32)n; i32 += stride) {
+#endif
     const u64 i = env_index(i32);
 #ifndef COG_NO_UNIFORM_PROOF
     const u32 parked = bcast(B.hidden[i * COG_HID_WORDS + COG_HL_ENV * 32 + COG_ES_PENDING], 0);

@@ -229,6 +229,7 @@ static inline unsigned __funnelshift_r(unsigned lo, unsigned hi, unsigned s) {
 }
 
 template <class T> static inline T __ldcg(const T *p) { return *p; } /* cache hints mean nothing here */
+static inline void __threadfence() { __asm__ __volatile__("" ::: "memory"); } /* warps run one after another */
 
 /* lanes run one at a time, so plain read-modify-write is atomic */
 template <class T> static inline T atomicOr(T *p, T v) { T o = *p; *p = o | v; return o; }
