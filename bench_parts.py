@@ -200,7 +200,10 @@ def roofline_fused(n, inner, k_ms, sm_mhz, stats):
                     "fused kernel keeps env state in registers for the whole launch, so the bytes never move (traffic "
                     "= real DRAM bytes per launch from the committed ncu capture) and the kernel is bound by "
                     "instruction issue: issue_frac = warp instructions per env-step (ncu) x env-steps/s / (148 SMs x "
-                    "4 schedulers x SM clock)"}
+                    "4 schedulers x SM clock). The *_ncu fields and the per-step instruction count come from the "
+                    "committed capture (profiles/r02_final_fused.txt), taken before the envs were handed out by "
+                    "ticket: same instructions per env-step, but the 0.79 issue_active of that capture is the static "
+                    "split's; issue_frac above is computed from this run's own rate"}
 
 
 # --------------------------------------------------------------------------- device-side extras
