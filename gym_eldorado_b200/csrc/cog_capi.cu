@@ -73,6 +73,9 @@ int cuda_fail(cudaError_t e, const char *what) {
 
 size_t scratch_bytes() { return sizeof(cog::BoardScratch) * cog::WARPS_PER_BLOCK; }
 unsigned blocks_for(uint64_t n) { return (unsigned)((n + cog::WARPS_PER_BLOCK - 1) / cog::WARPS_PER_BLOCK); }
+/* k_reset and k_step_single have block sizes of their own (COG_RESET_WARPS / COG_SINGLE_WARPS envs per block) */
+unsigned blocks_of(uint64_t n, unsigned warps) { return (unsigned)((n + warps - 1) / warps); }
+size_t scratch_of(unsigned warps) { return sizeof(cog::BoardScratch) * warps; }
 
 }  // namespace
 
@@ -174,7 +177,7 @@ bool use_pdl() {
 
 int launch_reset(cog_vec *h, uint32_t seed, int reseed) {
   CK(cudaSetDevice(h->device));
-  COG_LAUNCH(cog::k_reset, blocks_for(h->n), cog::BLOCK_THREADS, scratch_bytes(), h->stream, h->B, h->prm,
+  COG_LAUNCH(cog::k_reset, blocks_of(h->n, COG_RESET_WARPS), COG_RESET_WARPS * 32, scratch_of(COG_RESET_WARPS), h->stream, h->B, h->prm,
              h->n, (uint64_t)seed + h->offset, reseed);
   g_launches++;
   CK(cudaGetLastError());
@@ -257,11 +260,13 @@ template <bool SAMPLED>
 void launch_single(cog_vec *h, cudaStream_t stream, uint64_t i0, uint64_t i1, const void *actions,
                    uint32_t act_stride, void *masks2, void *pmasks, uint32_t *srng, uint8_t *actions_out) {
   if (use_pdl())
-    COG_LAUNCH_PDL(cog::k_step_single<SAMPLED>, blocks_for(i1 - i0), cog::BLOCK_THREADS, scratch_bytes(), stream, h->B,
+    COG_LAUNCH_PDL(cog::k_step_single<SAMPLED>, blocks_of(i1 - i0, COG_SINGLE_WARPS), COG_SINGLE_WARPS * 32,
+                   scratch_of(COG_SINGLE_WARPS), stream, h->B,
                    h->prm, i0, i1, (const uint8_t *)actions, act_stride, (uint8_t *)masks2, (uint8_t *)pmasks, srng,
                    actions_out);
   else
-    COG_LAUNCH(cog::k_step_single<SAMPLED>, blocks_for(i1 - i0), cog::BLOCK_THREADS, scratch_bytes(), stream, h->B,
+    COG_LAUNCH(cog::k_step_single<SAMPLED>, blocks_of(i1 - i0, COG_SINGLE_WARPS), COG_SINGLE_WARPS * 32,
+               scratch_of(COG_SINGLE_WARPS), stream, h->B,
                h->prm, i0, i1, (const uint8_t *)actions, act_stride, (uint8_t *)masks2, (uint8_t *)pmasks, srng,
                actions_out);
 }

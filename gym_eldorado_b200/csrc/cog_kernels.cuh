@@ -79,19 +79,27 @@ __device__ __forceinline__ void env_prove_uniform(Env &E) {
 
 /* vec_cog_env<N>::reset include/vec_environment.h:33-44.  reseed: env i restarts its RNG
  * from uint32(seed_base + i) (cog_env::reset(seed, ...) src/environment.cpp:66-77). */
+/* warps (= envs) per block of the kernels whose blocks the hardware scheduler hands out one env per warp: a block
+ * keeps its slot until its SLOWEST warp is done, and board generation times differ a lot between envs */
+#ifndef COG_RESET_WARPS
+#define COG_RESET_WARPS 4
+#endif
+#ifndef COG_SINGLE_WARPS
+#define COG_SINGLE_WARPS 4
+#endif
 #ifndef COG_RESET_BLOCKS
 #define COG_RESET_BLOCKS 12 /* with provably uniform control flow, occupancy beats spills: 7 blocks (72 registers) 1.39e8,
                              * 9 1.44e8, 12 (40 registers) 1.50e8, 14 / 16 (32) 1.49e8 resets/s (profiles/r02_y_resident_blocks.txt) */
 #endif
-__global__ void __launch_bounds__(BLOCK_THREADS, COG_RESET_BLOCKS) k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed) {
+__global__ void __launch_bounds__(COG_RESET_WARPS * 32, COG_RESET_BLOCKS) k_reset(Buffers B, Params prm, u64 n, u64 seed_base, int reseed) {
   const int lane = threadIdx.x & 31;
 #ifndef COG_NO_UNIFORM_PROOF
   /* warp index and env scalars through shuffles from a fixed lane: board generation is all warp-uniform
    * control flow, and ptxas only compiles it that way when it can prove it (see k_step_fused): 4 016 -> 2 800
    * instructions, BSSY 112 -> 26, BRA.DIV 41 -> 0; 1.21 -> 1.29e8 resets/s */
-  const u64 i = env_index(blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0));
+  const u64 i = env_index(blockIdx.x * COG_RESET_WARPS + bcast(threadIdx.x >> 5, 0));
 #else
-  const u64 i = env_index(blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5));
+  const u64 i = env_index(blockIdx.x * COG_RESET_WARPS + (threadIdx.x >> 5));
 #endif
   if (i >= n) return;
   Env E;
@@ -140,7 +148,7 @@ __device__ __forceinline__ void step_one_env(const Buffers &B, const Params &prm
  * current env is stepped — 65 536 atomics on one address per launch serialise in L2: 66 us per step of
  * 65 536 envs against 40 us, gpurun_out/r02_d_api_loop.txt.) */
 template <bool SAMPLED>
-__global__ void __launch_bounds__(BLOCK_THREADS, COG_SINGLE_BLOCKS) k_step_single(Buffers B, Params prm, u64 i0, u64 n,
+__global__ void __launch_bounds__(COG_SINGLE_WARPS * 32, COG_SINGLE_BLOCKS) k_step_single(Buffers B, Params prm, u64 i0, u64 n,
                                                                   const u8 *__restrict__ actions_in, u32 act_stride,
                                                                   u8 *masks2, u8 *pmasks, u32 *srng, u8 *actions_out) {
   const int lane = threadIdx.x & 31;
@@ -149,9 +157,9 @@ __global__ void __launch_bounds__(BLOCK_THREADS, COG_SINGLE_BLOCKS) k_step_singl
 #ifndef COG_NO_UNIFORM_PROOF
   /* as in k_step_fused: warp index and env scalars through shuffles from a fixed lane, so that
    * ptxas can prove them warp-uniform */
-  const u64 i = env_index((u32)i0 + blockIdx.x * WARPS_PER_BLOCK + bcast(threadIdx.x >> 5, 0));
+  const u64 i = env_index((u32)i0 + blockIdx.x * COG_SINGLE_WARPS + bcast(threadIdx.x >> 5, 0));
 #else
-  const u64 i = env_index((u32)i0 + blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5));
+  const u64 i = env_index((u32)i0 + blockIdx.x * COG_SINGLE_WARPS + (threadIdx.x >> 5));
 #endif
   if (i >= n) return;
   step_one_env<SAMPLED>(B, prm, i, actions_in, act_stride, masks2, pmasks, srng, actions_out, lane);
