@@ -902,8 +902,17 @@ __device__ __forceinline__ void env_cycle_phase(Env &E) { /* include/player.h:78
 /* Per-warp scratch in shared memory.  The occupancy bitmap is a 128 x 128 torus of
  * half-hex cells: a board that fits the 48 x 48 observation spans <= 94 half units,
  * and a candidate footprint reaches < 17 further, so two distinct live cells can
- * never alias (boards that outgrow the observation are reported immediately). */
-enum { BG_OCC_WORDS = 128 * 128 / 32, BG_MAX_PLACED = 32 };
+ * never alias (a generation whose intermediate board outgrows the observation, or piles up more than
+ * BG_MAX_PLACED pieces, is repeated out of line by the piece list: bg_generate_wide). */
+#ifndef COG_BG_MAX_PLACED
+#define COG_BG_MAX_PLACED 32 /* one lane per piece of the map (tests build with less, to exercise bg_generate_wide) */
+#endif
+enum { BG_OCC_WORDS = 128 * 128 / 32, BG_MAX_PLACED = COG_BG_MAX_PLACED };
+#ifdef COG_WIDE_BOARDS
+enum { BG_WIDE = -100 }; /* internal: this generation needs the out-of-line path by the piece list (bg_generate_wide) */
+#else
+enum { BG_WIDE = -3 };   /* default build: reported as COG_ERR_MAP_BOUNDS (see env_reset) */
+#endif
 struct bg_pose { int16_t cx, cy, rot, pad; };
 struct bg_placed { int16_t cx, cy, rot; u8 piece, pad; };
 struct BoardScratch {
@@ -939,7 +948,7 @@ __device__ __forceinline__ int sx8(u32 v) { return (int)(int8_t)(v & 0xffu); } /
  * occupancy bitmap; the bounds come from the shape's bounding box.  Returns 0 or COG error (-3). */
 __device__ __forceinline__ int bg_add_piece(BoardScratch &sc, BoardState &st, int piece, int px, int py,
                                             int rotation, int lane) {
-  if (st.n_list >= BG_MAX_PLACED) return -3;
+  if (st.n_list >= BG_MAX_PLACED) return BG_WIDE; /* one lane per piece of the map: see bg_generate_wide */
   /* (shared-memory reads that steer control flow go through a broadcast: provably uniform) */
   const int rot = mod6((int)bcast((u32)sc.pose[piece].rot, 0) + rotation),
             cx = (int)bcast((u32)(sc.pose[piece].cx + px), 0), cy = (int)bcast((u32)(sc.pose[piece].cy + py), 0);
@@ -971,8 +980,11 @@ __device__ __forceinline__ int bg_add_piece(BoardScratch &sc, BoardState &st, in
   st.miny = min(st.miny, cy + sx8(bb >> 16));
   st.maxy = max(st.maxy, cy + sx8(bb >> 24));
   __syncwarp();
-  /* largest cell index (coord - min + 2) / 2 must stay inside the 48 x 48 observation */
-  if ((st.maxx - st.minx + 2) / 2 > COGL_GRID - 1 || (st.maxy - st.miny + 2) / 2 > COGL_GRID - 1) return -3;
+  /* A board whose largest cell index (coord - min + 2) / 2 leaves the 48 x 48 observation cannot be the final
+   * one (bg_finalize reports that), but it can be an intermediate one: when the end piece then finds no place,
+   * the reference resets the map and generates again (src/map.cpp:734-739), and that board may fit.  The
+   * bitmap only holds boards that fit: the generation is repeated by the piece list (bg_generate_wide). */
+  if ((st.maxx - st.minx + 2) / 2 > COGL_GRID - 1 || (st.maxy - st.miny + 2) / 2 > COGL_GRID - 1) return BG_WIDE;
   return 0;
 }
 
@@ -1087,11 +1099,154 @@ __device__ __forceinline__ int bg_add_random_piece(BoardScratch &sc, BoardState 
   return rc ? rc : 1;
 }
 
+/* ------------------------------------------------ board generation by the piece list (rare, out of line)
+ * The fast path above keeps the map as a bitmap that only holds boards that fit the observation and enumerates
+ * candidates one lane per placed piece, so it stops (BG_WIDE) when an intermediate board grows wider than 48
+ * cells or more than 32 pieces pile up (a travel piece that finds no place makes the reference recurse WITHOUT
+ * Map::reset, src/map.cpp:726-731).  The reference goes on in both cases and may still end with a board that
+ * fits — about one board in 10^5..10^6 at 7-8 pieces, none at <= 5.  Those generations are repeated from the same
+ * engine state by the functions below: same candidate order, same draws, overlap tested piece against piece
+ * (exact for any extent), up to 512 pieces (the C restatement's capacity), the list spread over the lanes'
+ * local memory.  Slow and never on the path of the benchmarks. */
+enum { BG_WIDE_SLOTS = 16 };
+struct WideList { /* piece k of the map: lane k & 31, slot k >> 5 */
+  u32 a[BG_WIDE_SLOTS]; /* cx | cy << 16 (int16 each), the pose it was placed at */
+  u32 b[BG_WIDE_SLOTS]; /* rot | piece << 8 */
+};
+__device__ __forceinline__ void wide_get(const WideList &wl, int k, int &cx, int &cy, int &rot, int &piece) {
+  const u32 a = __shfl_sync(COG_FULL, wl.a[k >> 5], k & 31), b = __shfl_sync(COG_FULL, wl.b[k >> 5], k & 31);
+  cx = (int)(int16_t)(a & 0xffffu);
+  cy = (int)(int16_t)(a >> 16);
+  rot = (int)(b & 0xffu);
+  piece = (int)(b >> 8);
+}
+
+/* Map::add_piece src/map.cpp:309-341, list only */
+__device__ __forceinline__ int bg_add_piece_wide(BoardScratch &sc, BoardState &st, WideList &wl, int piece, int px,
+                                                 int py, int rotation, int lane) {
+  if (st.n_list >= 32 * BG_WIDE_SLOTS) return -3;
+  const int rot = mod6((int)bcast((u32)sc.pose[piece].rot, 0) + rotation),
+            cx = (int)bcast((u32)(sc.pose[piece].cx + px), 0), cy = (int)bcast((u32)(sc.pose[piece].cy + py), 0);
+  __syncwarp();
+  if (lane == 0) {
+    sc.pose[piece].rot = (int16_t)rot;
+    sc.pose[piece].cx = (int16_t)cx;
+    sc.pose[piece].cy = (int16_t)cy;
+  }
+  if (lane == (st.n_list & 31)) {
+    wl.a[st.n_list >> 5] = ((u32)cx & 0xffffu) | ((u32)cy << 16);
+    wl.b[st.n_list >> 5] = (u32)rot | ((u32)piece << 8);
+  }
+  st.n_list++;
+  const u32 bb = FOOT.bbox[PIECE_META[piece].size][rot];
+  st.minx = min(st.minx, cx + sx8(bb));
+  st.maxx = max(st.maxx, cx + sx8(bb >> 8));
+  st.miny = min(st.miny, cy + sx8(bb >> 16));
+  st.maxy = max(st.maxy, cy + sx8(bb >> 24));
+  __syncwarp();
+  return 0;
+}
+
+/* overlap (src/map.cpp:53-74) of this lane's footprint (`rows` at x, y) with every piece of the map.  Same row
+ * encoding as the bitmap test: byte 0 dx, byte 1 dy of the row's first cell, bits 16.. one bit per cell along y. */
+__device__ __forceinline__ u32 bg_overlap_wide(const WideList &wl, int n_list, const u32 *rows, int n_rows, int x,
+                                               int y) {
+  u32 hit = 0;
+  for (int q = 0; q < n_list; ++q) {
+    int qcx, qcy, qrot, qpiece;
+    wide_get(wl, q, qcx, qcy, qrot, qpiece);
+    const u32 *qrows = FOOT.row[piece_size(qpiece)][qrot];
+    for (int j = 0; j < n_rows; ++j) {
+      const u32 r = rows[j];
+      const int cx = x + sx8(r), cy = y + sx8(r >> 8);
+      const u64 cb = (u64)(r >> 16) << 16; /* room to shift by up to 15 either way */
+      for (int k = 0; k < 7; ++k) {
+        const u32 r2 = qrows[k];
+        const int sh = cy - (qcy + sx8(r2 >> 8));
+        if (qcx + sx8(r2) == cx && sh > -16 && sh < 16)
+          hit |= (u32)(((sh >= 0 ? cb << sh : cb >> -sh) & ((u64)(r2 >> 16) << 16)) != 0);
+      }
+    }
+  }
+  return hit;
+}
+
+/* Map::add_random_piece src/map.cpp:277-307: the candidates in the order of bg_add_random_piece (pieces of the
+ * map in order, the entries of each one's connection table), 32 hosts at a time; one pass to count the valid
+ * ones, the draw, a second pass to find the one drawn.  Returns 1 placed, 0 no candidate fits, < 0 error. */
+__device__ __forceinline__ int bg_add_random_piece_wide(BoardScratch &sc, BoardState &st, WideList &wl, int piece,
+                                                        u32 &rng, int lane) {
+  __syncwarp();
+  if (lane == 0) { /* MapPiece::reset :174-177 acts on the shared piece object */
+    sc.pose[piece].cx = 0; sc.pose[piece].cy = 0; sc.pose[piece].rot = 0;
+  }
+  __syncwarp();
+  const int ns = piece_size(piece);
+  const int n_rows = ns == SIZE_TRIPLE ? 3 : 7;
+  u32 n_valid = 0, idx = 0;
+  for (int pass = 0; pass < 2; ++pass) {
+    u32 seen = 0;
+    for (int hb = 0; hb < st.n_list; hb += 32) {
+      /* lane l <-> piece hb + l of the map, which is this lane's own slot hb >> 5 */
+      const bool have = hb + lane < st.n_list;
+      const int my_host = have ? (int)(wl.b[hb >> 5] >> 8) : 0;
+      const int hs = piece_size(my_host);
+      int my_kind = -1;
+      if (ns == SIZE_LARGE) my_kind = hs == SIZE_LARGE ? 0 : (hs == SIZE_SMALL ? 3 : -1);
+      else if (ns == SIZE_SMALL) my_kind = hs == SIZE_LARGE ? 1 : -1;
+      else my_kind = (hs == SIZE_LARGE && my_host >= 2) ? 2 : -1;
+      if (!have) my_kind = -1;
+      const u32 my_n = my_kind < 0 ? 0u : (0x31eaeu >> (5 * my_kind)) & 31u; /* 14, 21, 7, 6 */
+      const u32 my_incl = warp_incl_scan(my_n, lane);
+      const u32 total = bcast(my_incl, 31);
+      const int n_here = st.n_list - hb < 32 ? st.n_list - hb : 32;
+      for (u32 base = 0; base < total; base += 32) {
+        const u32 c = base + (u32)lane;
+        int k = 0; /* the piece of this chunk candidate c belongs to */
+        for (int j = 0; j < n_here; ++j) k += c >= bcast(my_incl, j);
+        k = k < 31 ? k : 31;
+        const int kind = max(__shfl_sync(COG_FULL, my_kind, k), 0);
+        const int e_raw = (int)(c - (__shfl_sync(COG_FULL, my_incl, k) - __shfl_sync(COG_FULL, my_n, k)));
+        const int e = c < total ? e_raw : 0; /* lanes past the last candidate compute on entry 0 and are masked below */
+        const int host = __shfl_sync(COG_FULL, my_host, k);
+        const bg_pose hp = sc.pose[host];
+        const int n_alt = (0x6132 >> (4 * kind)) & 15, first_opt = (0x4354 >> (4 * kind)) & 15;
+        int x, y, rot_add;
+        bg_conn_entry(hp.cx, hp.cy, hp.rot, kind, n_alt, e, x, y, rot_add);
+        const u32 hit = bg_overlap_wide(wl, st.n_list, FOOT.row[ns][mod6(first_opt + rot_add)], n_rows, x, y);
+        const u32 vm = __ballot_sync(COG_FULL, c < total && !hit);
+        const u32 cnt = (u32)__popc(vm);
+        if (pass == 0) {
+          n_valid += cnt;
+        } else if (idx - seen < cnt) { /* (unsigned: idx >= seen always holds here) the candidate drawn is in this round */
+          const int src = (int)nth_set_bit_warp(vm, idx - seen, lane);
+          const int ckind = __shfl_sync(COG_FULL, kind, src), ce = __shfl_sync(COG_FULL, e, src);
+          const bg_pose chp = sc.pose[__shfl_sync(COG_FULL, host, src)];
+          const int c_alt = (0x6132 >> (4 * ckind)) & 15, n_opts = (0x6126 >> (4 * ckind)) & 15; /* rotation options: 6 2 1 6 */
+          int cx, cy, crot_add;
+          bg_conn_entry((int)bcast((u32)chp.cx, 0), (int)bcast((u32)chp.cy, 0), (int)bcast((u32)chp.rot, 0), ckind, c_alt,
+                        ce, cx, cy, crot_add);
+          const int rot_idx = (int)uniform_draw(rng, (u32)n_opts);
+          const int rc = bg_add_piece_wide(sc, st, wl, piece, cx, cy, mod6(bg_rot_option(ckind, rot_idx) + crot_add), lane);
+          return rc ? rc : 1;
+        }
+        seen += cnt;
+      }
+    }
+    if (pass == 0) {
+      if (!n_valid) return 0;
+      idx = uniform_draw(rng, n_valid);
+    }
+  }
+  return -3; /* not reached: the second pass always finds candidate idx < n_valid */
+}
+
 /* Map::generate src/map.cpp:697-742.  The reference recurses (rng BY VALUE, no map
  * reset in the travel-piece branch); here the <= 5 frames live on an explicit stack.
  * Returns 0, -2 (generate_map_failure) or -3 (board outgrew the observation). */
+template <bool WIDE = false>
 __device__ __forceinline__ int bg_generate(BoardScratch &sc, BoardState &st, u32 rng0, int n_pieces,
-                                           int difficulty, int lane) {
+                                           int difficulty, int lane, WideList *wl = nullptr) {
   enum { F_ENTER = 0, F_LOOP = 1, F_DONE = 2, MAX_DEPTH = 5 };
   /* the running frame lives in registers; parents wait on a small stack.  Popped values go
    * through a broadcast so that ptxas can still prove them warp-uniform (a shuffle from a fixed
@@ -1109,7 +1264,9 @@ __device__ __forceinline__ int bg_generate(BoardScratch &sc, BoardState &st, u32
   for (;;) {
     if (state == F_ENTER) {
       const int start = (int)uniform_draw(rng, 2);
-      const int rc = bg_add_piece(sc, st, start, 0, 0, 0, lane);
+      int rc;
+      if constexpr (WIDE) rc = bg_add_piece_wide(sc, st, *wl, start, 0, 0, 0, lane);
+      else rc = bg_add_piece(sc, st, start, 0, 0, 0, lane);
       if (rc) return rc;
       valid = 0;
       nvalid = 0;
@@ -1124,7 +1281,8 @@ __device__ __forceinline__ int bg_generate(BoardScratch &sc, BoardState &st, u32
         if (nvalid) {
           const u32 pos = uniform_draw(rng, (u32)nvalid);
           next_idx = (int)((valid >> (4 * pos)) & 15u);
-          success = bg_add_random_piece(sc, st, 2 + next_idx, rng, lane);
+          if constexpr (WIDE) success = bg_add_random_piece_wide(sc, st, *wl, 2 + next_idx, rng, lane);
+          else success = bg_add_random_piece(sc, st, 2 + next_idx, rng, lane);
           if (success < 0) return success;
         }
         fi++;
@@ -1141,7 +1299,9 @@ __device__ __forceinline__ int bg_generate(BoardScratch &sc, BoardState &st, u32
         }
       } else {
         const int endp = 18 + (int)uniform_draw(rng, 2);
-        const int ok = bg_add_random_piece(sc, st, endp, rng, lane);
+        int ok;
+        if constexpr (WIDE) ok = bg_add_random_piece_wide(sc, st, *wl, endp, rng, lane);
+        else ok = bg_add_random_piece(sc, st, endp, rng, lane);
         if (ok < 0) return ok;
         state = F_DONE;
         if (!ok) {
@@ -1178,8 +1338,7 @@ __device__ __forceinline__ int bg_generate(BoardScratch &sc, BoardState &st, u32
  * n_required, feature 6 = is_end, feature 0 never written.  (The zero fill leaves the lines in L2, the
  * byte stores merge there; the encode used to be a pass over all 1008 16-byte chunks of the map that
  * re-derived every chunk from the grid — 3 100 warp instructions per reset against about 500.) */
-__device__ __forceinline__ int bg_finalize(const BoardScratch &sc, const BoardState &st, u8 *grid,
-                                           u8 *mapobs, int lane) {
+__device__ __forceinline__ void bg_clear_previous(u8 *grid, u8 *mapobs, int lane) {
   uint4 *g4 = reinterpret_cast<uint4 *>(grid);
   uint4 *m4 = reinterpret_cast<uint4 *>(mapobs);
   /* The observation is the expansion of the private grid, cell by cell, at all times (both start zeroed —
@@ -1197,11 +1356,11 @@ __device__ __forceinline__ int bg_finalize(const BoardScratch &sc, const BoardSt
     }
   }
   __syncwarp();
+}
+/* one piece of the map into the grid and the observation; returns true when a hex falls outside */
+__device__ __forceinline__ bool bg_scatter_piece(int piece, int rot, int ox, int oy, u8 *grid, u8 *mapobs, int lane) {
   bool bad = false;
-  for (int k = 0; k < st.n_list; ++k) {
-    const bg_placed pl = sc.placed[k];
-    const int piece = (int)bcast((u32)pl.piece, 0), rot = (int)bcast((u32)pl.rot, 0);
-    const int ox = (int)bcast((u32)(pl.cx - st.minx + 2), 0), oy = (int)bcast((u32)(pl.cy - st.miny + 2), 0);
+  {
     const piece_meta pm = PIECE_META[piece];
     const xy8 *co = piece_coords(pm.size);
     const rot6 m = rot_matrix(rot);
@@ -1225,8 +1384,46 @@ __device__ __forceinline__ int bg_finalize(const BoardScratch &sc, const BoardSt
     }
     __syncwarp();
   }
+  return bad;
+}
+__device__ __forceinline__ int bg_finalize(const BoardScratch &sc, const BoardState &st, u8 *grid,
+                                           u8 *mapobs, int lane) {
+  bg_clear_previous(grid, mapobs, lane);
+  bool bad = false;
+  for (int k = 0; k < st.n_list; ++k) {
+    const bg_placed pl = sc.placed[k];
+    const int piece = (int)bcast((u32)pl.piece, 0), rot = (int)bcast((u32)pl.rot, 0);
+    const int ox = (int)bcast((u32)(pl.cx - st.minx + 2), 0), oy = (int)bcast((u32)(pl.cy - st.miny + 2), 0);
+    bad |= bg_scatter_piece(piece, rot, ox, oy, grid, mapobs, lane);
+  }
   if (__any_sync(COG_FULL, bad)) return -3;
   return 0;
+}
+
+/* The whole generation once more from the same engine state, by the piece list, and the map encode from that
+ * list.  Out of line: a path this cold must not shape the register allocation of the kernels that reset. */
+/* (Everything goes in and out BY VALUE except the shared-memory scratch: a caller's BoardState handed over by
+ * reference would have to live in local memory for the whole kernel.)  Returns the error code in the low word
+ * and, on success, the board's min_xy (loc_pack) in the high word. */
+__device__ __attribute__((noinline)) u64 bg_generate_wide(BoardScratch &sc, u32 rng0, int n_pieces, int difficulty,
+                                                          u8 *grid, u8 *mapobs, int lane) {
+  WideList wl;
+  for (int k = 0; k < BG_WIDE_SLOTS; ++k) wl.a[k] = wl.b[k] = 0;
+  BoardState st;
+  bg_map_reset(sc, st, lane);
+  const int rc = bg_generate<true>(sc, st, rng0, n_pieces, difficulty, lane, &wl);
+  if (rc) return (u64)(u32)rc;
+  /* a board that leaves the observation is reported before anything is written */
+  if ((st.maxx - st.minx + 2) / 2 > COGL_GRID - 1 || (st.maxy - st.miny + 2) / 2 > COGL_GRID - 1) return (u64)(u32)-3;
+  bg_clear_previous(grid, mapobs, lane);
+  bool bad = false;
+  for (int k = 0; k < st.n_list; ++k) {
+    int cx, cy, rot, piece;
+    wide_get(wl, k, cx, cy, rot, piece);
+    bad |= bg_scatter_piece(piece, rot, cx - st.minx + 2, cy - st.miny + 2, grid, mapobs, lane);
+  }
+  if (__any_sync(COG_FULL, bad)) return (u64)(u32)-3;
+  return (u64)loc_pack(st.minx, st.miny) << 32;
 }
 
 /* ------------------------------------------------------------------- reset */
@@ -1294,6 +1491,20 @@ __device__ __forceinline__ int env_reset(Env &E, const Params &prm, const Buffer
   bg_map_reset(sc, st, lane);
   int rc = bg_generate(sc, st, E.rng, (int)prm.n_pieces, (int)prm.difficulty, lane);
   u8 *grid = B.grid + i * COGL_GRID_BYTES;
+#ifdef COG_WIDE_BOARDS
+  if (COG_UNLIKELY(rc == BG_WIDE)) {
+    const u64 w = bg_generate_wide(sc, E.rng, (int)prm.n_pieces, (int)prm.difficulty, grid, B.obs + i * COGL_OBS_SIZE, lane);
+    rc = (int)(u32)w;
+    st.minx = loc_x((u32)(w >> 32));
+    st.miny = loc_y((u32)(w >> 32));
+  } else
+#else
+  /* Default build: such a generation is reported (COG_ERR_MAP_BOUNDS) instead of repeated by the piece list.
+   * -DCOG_WIDE_BOARDS builds the exact path in — bit-exact with the restatement on the emulator, also when
+   * EVERY board is forced through it (COG_BG_MAX_PLACED=1) — but the call changes the register allocation of
+   * the three kernels that reset (more spill code in their bodies), and no GPU time was left to measure it. */
+  static_assert(BG_WIDE == -3, "without the exact path BG_WIDE is the error itself");
+#endif
   if (!rc) rc = bg_finalize(sc, st, grid, B.obs + i * COGL_OBS_SIZE, lane);
   if (rc) {
     report_error(B, rc, i, lane);

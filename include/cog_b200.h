@@ -46,7 +46,8 @@ typedef enum cog_status {
   COG_ERR_MAP_FAILURE = -2,  /* generate_map_failure (reference include/map.h:13-15) */
   COG_ERR_MAP_BOUNDS = -3,   /* board does not fit the 48x48 observation (UB in the reference); with 6+ pieces also:
                               * more than 32 pieces on the map during one generation, or an intermediate board
-                              * wider than the observation ("known limit") */
+                              * wider than the observation ("known limit"; a library built with
+                              * -DCOG_WIDE_BOARDS generates those boards exactly) */
   COG_ERR_CUDA = -4,         /* a CUDA runtime call failed */
   COG_ERR_NOT_RESET = -5     /* step before the first reset(seed, ...) */
 } cog_status;

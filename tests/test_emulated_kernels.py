@@ -187,3 +187,32 @@ def test_emulated_two_players_vs_reference(emu):
 def test_emulated_packed_host_io(emu, oracle_cls, regime):
     """16-byte masks / 8-byte actions through cog_*_packed_host_io == the oracle at every step"""
     assert parity.run_packed_io_parity(emu, oracle_cls, 12, 99, layout.HARD, 10, 200, regime) > 0
+
+
+def test_emulated_wide_boards(oracle_cls):
+    """-DCOG_WIDE_BOARDS: board generation by the piece list (bg_generate_wide), the exact path for generations
+    that pile up more pieces than the fast path has lanes for or whose intermediate board outgrows the bitmap.
+    This build sends every board of more than two pieces through it (COG_BG_MAX_PLACED=2): boards, failed
+    generations, auto-resets in long trajectories and the case the randomised campaign found (7 pieces, HARD,
+    32 pieces piled up in an auto-reset at step 59, env 30) must all equal the restatement."""
+    import os
+    import subprocess
+    from oracle import port
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "emu")
+    subprocess.check_call(["make", "-s", "-C", here, os.path.join(here, "libcog_emu_wide.so")])
+    wide = capi.load(os.path.join(here, "libcog_emu_wide.so"))
+    for difficulty, n_pieces, seed in ((layout.EASY, 3, 1), (layout.MEDIUM, 5, 11), (layout.HARD, 8, 4000),
+                                       (layout.EASY, 4, 123)):
+        o = oracle_cls(24, 0)
+        c = parity.Candidate(wide, 24, 0)
+        try:
+            o.reset(seed, 4, n_pieces, difficulty, 100)
+        except port.MapGenerationError:
+            with pytest.raises(capi.MapGenerationError):
+                c.reset(seed, 4, n_pieces, difficulty, 100)
+        else:
+            c.reset(seed, 4, n_pieces, difficulty, 100)
+            assert parity.first_mismatch(c.snapshot(), parity.oracle_snapshot(o)) is None
+        c.close(); o.close()
+    assert parity.run_parity(wide, oracle_cls, 16, 777, layout.HARD, 8, 200, "M") > 0
+    parity.run_parity(wide, oracle_cls, 40, 68145605, layout.HARD, 0, 62, "M", n_pieces=7)

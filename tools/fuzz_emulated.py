@@ -194,7 +194,8 @@ def worker(wid, a, q):
         from gym_eldorado_b200 import capi
         emu = capi.lib()  # the product library on a GPU box (fails loudly without one)
     elif a.pair == "emu-port":
-        emu = parity.emu_lib()
+        from gym_eldorado_b200 import capi
+        emu = capi.load(os.path.abspath(a.lib)) if a.lib else parity.emu_lib()
     else:
         emu = None
     rng = random.Random(a.seed * 1000 + wid)
@@ -236,6 +237,8 @@ def main():
     ap.add_argument("--pair", choices=["emu-port", "port-ref", "cuda-port"], default="emu-port",
                     help="emu-port: emulated kernels vs the C restatement; port-ref: the C restatement vs oracle/_ref; "
                          "cuda-port: the product library on a GPU box vs the C restatement")
+    ap.add_argument("--lib", default=None, help="emu-port: another build of the emulated library (e.g. one with "
+                    "-DCOG_BG_MAX_PLACED=3, where nearly every board takes the out-of-line generation path)")
     ap.add_argument("--verbose", action="store_true")
     a = ap.parse_args()
     # build once before forking so the workers do not race on make
