@@ -161,18 +161,32 @@ def run_case_port_vs_reference(case):
                 m = parity.player_masks(snap) if regime == "P" else parity.merged_masks(snap)
                 o.sample(m); r.sample(m)
             failed = [False, False]
+            why = ""
             for k, side in enumerate((o, r)):
                 try:
                     side.step()
-                except (port.MapGenerationError, RuntimeError):
+                except (port.MapGenerationError, RuntimeError) as e:
                     failed[k] = True
+                    why = why or str(e)
+            if failed[0] and not failed[1] and "exceeds the 48x48" in why:
+                # the board does not fit the observation: the reference writes outside it (undefined behaviour,
+                # silent here), the restatement reports it — the documented difference
+                return "ref_ub_board_outgrows_observation"
             assert failed[0] == failed[1], "auto-reset board generation: port failed=%s reference failed=%s" % tuple(failed)
             if failed[0]:
                 return "ref_map_failure_later"
             bad = parity.first_mismatch(parity.oracle_snapshot(o), parity.oracle_snapshot(r))
             assert bad is None, "step %d: %s" % (s, bad)
             if case["mode"] == "midreset" and s == case["steps"] // 2:
-                o.reset(); r.reset()
+                failed = [False, False]
+                for k, side in enumerate((o, r)):
+                    try:
+                        side.reset()
+                    except (port.MapGenerationError, RuntimeError):
+                        failed[k] = True
+                assert failed[0] == failed[1], "mid-episode reset(): port failed=%s reference failed=%s" % tuple(failed)
+                if failed[0]:
+                    return "ref_map_failure_later"
                 bad = parity.first_mismatch(parity.oracle_snapshot(o), parity.oracle_snapshot(r))
                 assert bad is None, "right after reset(): " + bad
     finally:
