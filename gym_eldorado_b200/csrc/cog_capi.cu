@@ -938,7 +938,7 @@ int cog_vec_run_fused_ex(cog_vec *h, cog_sampler *s, uint64_t k_steps, int mask_
     return fail(COG_ERR_INVALID, "the fused loop needs auto-reset (cog_vec_set_autoreset(h, 1))");
   CK(cudaSetDevice(h->device));
   if (s->stream != h->stream) CK(cudaStreamSynchronize(s->stream));
-  /* persistent grid: every SM filled once, warps walk the envs with a grid stride */
+  /* persistent grid: every SM filled once, the warps draw their envs from a ticket counter (k_step_fused) */
   unsigned grid = blocks_for(h->n);
   const unsigned resident = (unsigned)(h->sm_count * h->fused_blocks_per_sm);
   if (grid > resident) grid = resident;

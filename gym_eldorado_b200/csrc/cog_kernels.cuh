@@ -291,7 +291,7 @@ __device__ __forceinline__ void store_action(u8 *actions_out, u64 i, u32 act, u3
 }
 
 /* Persistent fused path: k_steps x {vec_sampler.sample(selected masks); vec_env.step} with
- * no host round trip.  Each warp walks envs with a grid stride and keeps the env in
+ * no host round trip.  Each warp takes envs from a ticket counter, one at a time, and keeps the env in
  * registers for all its iterations.
  *
  * Two kernels per launch.  k_step_fused is the hot loop and contains no episode-end code:
