@@ -1104,7 +1104,7 @@ __device__ __forceinline__ int bg_add_random_piece(BoardScratch &sc, BoardState 
  * candidates one lane per placed piece, so it stops (BG_WIDE) when an intermediate board grows wider than 48
  * cells or more than 32 pieces pile up (a travel piece that finds no place makes the reference recurse WITHOUT
  * Map::reset, src/map.cpp:726-731).  The reference goes on in both cases and may still end with a board that
- * fits — about one board in 10^5..10^6 at 7-8 pieces, none at <= 5.  Those generations are repeated from the same
+ * fits — met once in about half a million boards of 6-8 pieces, never at <= 5.  Those generations are repeated from the same
  * engine state by the functions below: same candidate order, same draws, overlap tested piece against piece
  * (exact for any extent), up to 512 pieces (the C restatement's capacity), the list spread over the lanes'
  * local memory.  Slow and never on the path of the benchmarks. */
