@@ -44,7 +44,7 @@ typedef enum cog_status {
   COG_OK = 0,
   COG_ERR_INVALID = -1,      /* bad argument / handle */
   COG_ERR_MAP_FAILURE = -2,  /* generate_map_failure (reference include/map.h:13-15) */
-  COG_ERR_MAP_BOUNDS = -3,   /* board does not fit the 48x48 observation (UB in the reference); with 6+ pieces also:
+  COG_ERR_MAP_BOUNDS = -3,   /* board does not fit the 48x48 observation (UB in the reference); rarely (seen at 7 pieces) also:
                               * more than 32 pieces on the map during one generation, or an intermediate board
                               * wider than the observation ("known limit"; a library built with
                               * -DCOG_WIDE_BOARDS generates those boards exactly) */
